@@ -1,0 +1,119 @@
+/* radiosim_b200 -- C ABI of the B200-native image-synthesis hot path.
+ *
+ * The reference (radionets-project/radiosim) is pure Python and has no FFI layer;
+ * this library is the NEW layer underneath its generator functions.  Each entry
+ * point below names the reference code whose pixel work it replaces
+ * (paths relative to the reference checkout, e.g. src/radiosim/jets/jet.py:145).
+ *
+ * Conventions
+ *  - plain C: pointers and sizes only, no C++/torch types.
+ *  - every function returns 0 on success, a negative value for a CUDA error and a
+ *    positive value for an argument error; rsb_last_error() describes the last
+ *    failure on the calling thread.
+ *  - "dev" pointers are device pointers on the current device, "host" pointers are
+ *    host memory (pinned memory from rsb_malloc_host gives full PCIe bandwidth).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *    Device-pointer entry points only enqueue work; they do not synchronise.
+ *  - there is no CPU fallback: without a CUDA device every compute entry fails.
+ */
+#ifndef RADIOSIM_B200_H
+#define RADIOSIM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RSB_ABI_VERSION 1
+
+/* ------------------------------------------------------------------ runtime */
+int rsb_abi_version(void);
+const char* rsb_last_error(void);
+int rsb_device_count(int* count);
+int rsb_set_device(int device);
+int rsb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor,
+                    size_t* total_mem);
+int rsb_malloc(void** dev_ptr, size_t bytes);
+int rsb_free(void* dev_ptr);
+int rsb_malloc_host(void** host_ptr, size_t bytes); /* pinned */
+int rsb_free_host(void* host_ptr);
+int rsb_memset(void* dev_ptr, int value, size_t bytes, void* stream);
+int rsb_memcpy_h2d(void* dev_dst, const void* host_src, size_t bytes, void* stream);
+int rsb_memcpy_d2h(void* host_dst, const void* dev_src, size_t bytes, void* stream);
+int rsb_stream_create(void** stream);
+int rsb_stream_destroy(void* stream);
+int rsb_stream_sync(void* stream);
+int rsb_device_sync(void);
+int rsb_event_create(void** event);
+int rsb_event_destroy(void* event);
+int rsb_event_record(void* event, void* stream);
+int rsb_event_elapsed_ms(void* start, void* stop, float* ms); /* syncs on stop */
+/* kernels launched by this library since load (all devices, this process) */
+int rsb_launch_count(uint64_t* count);
+
+/* Micro-benchmark: sustained MUFU.EX2 rate of the current device in ex2/s (best of
+ * 5 launches of `iters` dependent ex2 x 8 chains per thread, CUDA events).  It is the
+ * roofline denominator of the exp-bound splat kernels; no reference counterpart. */
+int rsb_bench_sfu(int iters, double* ex2_per_second);
+
+/* --------------------------------------------------------------------- jets */
+/* Layout of one jet's parameters: `slots` components, each 6 float64 in the
+ * order the reference hands to twodgaussian (src/radiosim/jets/jet.py:255-258):
+ *   [amp, x (column centre), y (row centre), sx, sy, rotation].
+ * A slot with amp == 0 is skipped (jet.py:252-253).  params is [n][slots][6]. */
+#define RSB_JET_PARAM_STRIDE 6
+#define RSB_JET_MAX_SLOTS 64
+
+/* flags for rsb_jet_render* */
+#define RSB_JET_NORMALIZE 1u /* conf.jet.scaling == "normalize" (jet.py:177-181) */
+#define RSB_JET_OUT_F64 2u   /* out_img is float64 (the reference dtype), else float32 */
+
+/* Bytes of device scratch rsb_jet_render needs for n images of size x size
+ * (0 when the image fits in shared memory). */
+int rsb_jet_workspace_bytes(int n, int slots, int size, size_t* bytes);
+
+/* Render n jets -- replaces, per image, component_from_list + plane sum
+ * (src/radiosim/jets/jet.py:145-146, :234-261, src/radiosim/utils/gauss.py:50-97),
+ * zoom_on_source (src/radiosim/utils/utils.py:90-138), zoom_out (:141-177, image
+ * only -- the reference leaves the planes untouched) and the max-normalisation
+ * (jet.py:177-181).
+ *
+ *  params_dev   [n][slots][6] float64
+ *  zoom_pad_dev [n] int32: < 0  -> the edge test (jet.py:149-157, evaluated by the
+ *               host packer because it gates an RNG draw) failed: no zoom;
+ *               >= 0 -> zoom branch, value = int64(pad_value) of jet.py:169-170.
+ *  out_img_dev  [n][size][size] float32 (or float64 with RSB_JET_OUT_F64)
+ *  out_margin_dev [n] int32: idx of zoom_on_source (utils.py:119), 0 when not zoomed
+ *  out_peak_dev [n] float64: jet_max (jet.py:178) when RSB_JET_NORMALIZE, else 1.
+ *               Evaluated in float64 at the float32 arg-max pixel.
+ *  workspace_dev / workspace_bytes: >= rsb_jet_workspace_bytes(); may be NULL/0
+ *               when that is 0.
+ */
+int rsb_jet_render(const double* params_dev, const int32_t* zoom_pad_dev, int n,
+                   int slots, int size, unsigned flags, void* out_img_dev,
+                   int32_t* out_margin_dev, double* out_peak_dev, void* workspace_dev,
+                   size_t workspace_bytes, void* stream);
+
+/* Component planes for training_type == "gauss" (jet.py:185, :219-225): the
+ * `slots` planes after zoom_on_source (NOT zoomed out -- utils.py:168-175 drops
+ * that result), divided by peak.  margin/peak come from rsb_jet_render.
+ *  out_planes_dev [n][slots][size][size] float32/float64 (RSB_JET_OUT_F64) */
+int rsb_jet_planes(const double* params_dev, const int32_t* zoom_pad_dev,
+                   const int32_t* margin_dev, const double* peak_dev, int n, int slots,
+                   int size, unsigned flags, void* out_planes_dev, void* stream);
+
+/* Host-buffer convenience (the call a ctypes user makes): copies params in,
+ * renders in chunks on internal streams with copy/compute overlap, copies images,
+ * margins and peaks back, and synchronises.  Buffers should be pinned
+ * (rsb_malloc_host) for full PCIe bandwidth; pageable memory works but is slower.
+ * Allocates and caches device staging buffers on first use. */
+int rsb_jet_render_host(const double* params_host, const int32_t* zoom_pad_host, int n,
+                        int slots, int size, unsigned flags, void* out_img_host,
+                        int32_t* out_margin_host, double* out_peak_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RADIOSIM_B200_H */

@@ -1,0 +1,182 @@
+"""ctypes binding of ``librsb200.so`` (declared in ``include/radiosim_b200.h``).
+
+There is no CPU fallback: importing this module without the built library, or
+calling a compute entry point without a CUDA device, raises.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librsb200.so")
+
+JET_NORMALIZE = 1
+JET_OUT_F64 = 2
+
+
+class RsbError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m radiosim_b200.build` "
+            "(needs nvcc; there is no CPU fallback)"
+        )
+    return C.CDLL(LIB_PATH)
+
+
+_lib = _load()
+
+_vp, _i32, _u32, _sz = C.c_void_p, C.c_int, C.c_uint, C.c_size_t
+_SIGS = {
+    "rsb_abi_version": ([], _i32),
+    "rsb_last_error": ([], C.c_char_p),
+    "rsb_device_count": ([C.POINTER(_i32)], _i32),
+    "rsb_set_device": ([_i32], _i32),
+    "rsb_device_info": ([_i32, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_sz)], _i32),
+    "rsb_malloc": ([C.POINTER(_vp), _sz], _i32),
+    "rsb_free": ([_vp], _i32),
+    "rsb_malloc_host": ([C.POINTER(_vp), _sz], _i32),
+    "rsb_free_host": ([_vp], _i32),
+    "rsb_memset": ([_vp, _i32, _sz, _vp], _i32),
+    "rsb_memcpy_h2d": ([_vp, _vp, _sz, _vp], _i32),
+    "rsb_memcpy_d2h": ([_vp, _vp, _sz, _vp], _i32),
+    "rsb_stream_create": ([C.POINTER(_vp)], _i32),
+    "rsb_stream_destroy": ([_vp], _i32),
+    "rsb_stream_sync": ([_vp], _i32),
+    "rsb_device_sync": ([], _i32),
+    "rsb_event_create": ([C.POINTER(_vp)], _i32),
+    "rsb_event_destroy": ([_vp], _i32),
+    "rsb_event_record": ([_vp, _vp], _i32),
+    "rsb_event_elapsed_ms": ([_vp, _vp, C.POINTER(C.c_float)], _i32),
+    "rsb_launch_count": ([C.POINTER(C.c_uint64)], _i32),
+    "rsb_bench_sfu": ([_i32, C.POINTER(C.c_double)], _i32),
+    "rsb_jet_workspace_bytes": ([_i32, _i32, _i32, C.POINTER(_sz)], _i32),
+    "rsb_jet_render": ([_vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp, _vp, _sz, _vp], _i32),
+    "rsb_jet_planes": ([_vp, _vp, _vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp], _i32),
+    "rsb_jet_render_host": ([_vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp], _i32),
+}
+for _name, (_args, _res) in _SIGS.items():
+    if hasattr(_lib, _name):
+        _f = getattr(_lib, _name)
+        _f.argtypes = _args
+        _f.restype = _res
+
+EXPORTS = tuple(_SIGS)
+
+
+def lib():
+    return _lib
+
+
+def check(code: int, what: str = "") -> None:
+    if code != 0:
+        msg = _lib.rsb_last_error().decode(errors="replace")
+        raise RsbError(f"{what or 'librsb200'} failed ({code}): {msg}")
+
+
+def device_count() -> int:
+    n = _i32(0)
+    if _lib.rsb_device_count(C.byref(n)) != 0:
+        return 0
+    return n.value
+
+
+def require_device() -> None:
+    if device_count() < 1:
+        raise RsbError(
+            "radiosim_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback: "
+            + _lib.rsb_last_error().decode(errors="replace")
+        )
+
+
+def set_device(dev: int) -> None:
+    check(_lib.rsb_set_device(int(dev)), "rsb_set_device")
+
+
+def launch_count() -> int:
+    n = C.c_uint64(0)
+    check(_lib.rsb_launch_count(C.byref(n)))
+    return n.value
+
+
+def device_sync() -> None:
+    check(_lib.rsb_device_sync(), "rsb_device_sync")
+
+
+class DeviceBuffer:
+    """Owning handle of a device allocation (rsb_malloc / rsb_free)."""
+
+    def __init__(self, nbytes: int):
+        p = _vp()
+        check(_lib.rsb_malloc(C.byref(p), int(nbytes)), "rsb_malloc")
+        self.ptr = p.value
+        self.nbytes = int(nbytes)
+
+    def free(self):
+        if getattr(self, "ptr", None):
+            _lib.rsb_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def upload(self, arr: np.ndarray, stream=None):
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes <= self.nbytes
+        check(_lib.rsb_memcpy_h2d(self.ptr, arr.ctypes.data, arr.nbytes, stream), "h2d")
+        if stream is None:
+            device_sync()
+        return self
+
+    def download(self, shape, dtype, stream=None) -> np.ndarray:
+        out = np.empty(shape, dtype=dtype)
+        assert out.nbytes <= self.nbytes
+        check(_lib.rsb_memcpy_d2h(out.ctypes.data, self.ptr, out.nbytes, stream), "d2h")
+        device_sync()
+        return out
+
+
+class _PinnedOwner:
+    def __init__(self, nbytes):
+        p = _vp()
+        check(_lib.rsb_malloc_host(C.byref(p), int(nbytes)), "rsb_malloc_host")
+        self.ptr = p.value
+        self.nbytes = int(nbytes)
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                _lib.rsb_free_host(self.ptr)
+                self.ptr = None
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """numpy array backed by page-locked host memory.
+
+    The allocation is owned by the ctypes buffer at the ROOT of the array's base
+    chain, so it outlives every view numpy derives from the array.
+    """
+    dtype = np.dtype(dtype)
+    count = int(np.prod(shape))
+    nbytes = count * dtype.itemsize
+    owner = _PinnedOwner(nbytes)
+    buf = (C.c_char * max(nbytes, 1)).from_address(owner.ptr)
+    buf._rsb_owner = owner
+    return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+
+def dev_from(arr: np.ndarray) -> DeviceBuffer:
+    arr = np.ascontiguousarray(arr)
+    return DeviceBuffer(max(arr.nbytes, 16)).upload(arr)

@@ -1,0 +1,799 @@
+// Fused jet renderer: splat -> margin -> zoom-in -> zoom-out -> max-normalise.
+//
+// One persistent CTA renders one image at a time.  Per image:
+//   setup   : the [slots][6] float64 parameter block arrives by a 1-D bulk async
+//             copy (TMA engine, double-buffered so the next image's block is in
+//             flight while this one renders); warp 0 turns it into float32 conic
+//             coefficients + bounding boxes (culling) for the live slots.
+//   phase 1 : every warp renders (row, 128-column strip) items, 4 pixels per lane,
+//             one MUFU.EX2 + 3 FFMA + 1 FADD per pixel-component, components whose
+//             1e-8 footprint misses the strip are skipped warp-uniformly.  The raw
+//             image is kept on chip (shared memory) or, when size*size*4 exceeds
+//             shared memory, in an L2-resident per-CTA global scratch slot.
+//   zoom    : (only when the host edge test says so) margin = min border distance
+//             of pixels > 0.01 (borderline pixels re-evaluated in float64); the
+//             two cv2.resize(INTER_LINEAR) calls of the reference collapse into ONE
+//             separable 4-tap operator per axis, applied in place (H pass) and on
+//             the fly (V pass, run twice: once for the maximum, once to write).
+//   output  : every pixel is written exactly once with 128-bit stores, already
+//             divided by the image maximum.
+//
+// Reference: src/radiosim/jets/jet.py:144-181, src/radiosim/utils/gauss.py:50-97,
+// src/radiosim/utils/utils.py:90-177.
+#include <cmath>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+
+namespace rsb {
+namespace jet {
+
+constexpr int kThreads = 512;
+constexpr int kWarps = kThreads / 32;
+constexpr int kStrip = 128;  // columns per warp strip: 4 per lane
+constexpr int kMaxSlots = RSB_JET_MAX_SLOTS;
+constexpr int kCtasPerSm = 2;
+constexpr double kEdgeThr = 0.01;  // jet.py:156 / utils.py:90 max_amp
+
+// float32 coefficients of one live component (read warp-uniformly).
+//   g(r,c) = amp * 2^(A dc^2 + B dc dr + C dr^2),  dc = c - xc, dr = r - yc
+struct __align__(16) Coef {
+  float A, B, C, amp;
+  float irf, fr, icf, fc;  // centre split into integer part and fraction
+  int r0, r1, c0, c1;      // inclusive bounding box of the > tau footprint
+};
+
+struct Args {
+  const double* params;
+  const int32_t* zoom_pad;
+  int n, slots, size;
+  unsigned flags;
+  void* out;
+  int32_t* margin;
+  double* peak;
+  float* scratch;  // per-CTA raw-image slots when the image does not fit in smem
+  int pitch;       // floats per stored raw row (size rounded up to 4)
+};
+
+struct __align__(16) Fixed {
+  double params[2][kMaxSlots * RSB_JET_PARAM_STRIDE];
+  Coef coef[kMaxSlots];
+  double red_d[kWarps];
+  unsigned long long red_u[kWarps];
+  uint64_t bar[2];
+  double peak;
+  double pix64[16];
+  int red_i[kWarps];
+  int nlive;
+  int margin;
+  unsigned long long best;
+  float delta;
+};
+
+// ---- float64 evaluation of one raw pixel, operation order of gauss.py:77-88 ----
+__device__ double eval64(const double* P, int slots, int r, int c) {
+  double sum = 0.0;
+  for (int k = 0; k < slots; ++k) {
+    const double* p = P + k * RSB_JET_PARAM_STRIDE;
+    const double amp = p[0];
+    if (amp == 0.0) continue;
+    const double cr = cos(p[5]), sr = sin(p[5]);
+    const double ra = p[2] * cr - p[1] * sr;
+    const double rb = p[2] * sr + p[1] * cr;
+    const double ua = r * cr - c * sr;
+    const double ub = r * sr + c * cr;
+    const double a = (ra - ua) / p[4];
+    const double b = (rb - ub) / p[3];
+    sum += amp * exp(-(a * a + b * b) / 2.0);
+  }
+  return sum;
+}
+
+// ---- composite 4-tap operator of zoom_on_source followed by zoom_out -------------
+// cv2.resize INTER_LINEAR per axis: f = (d+0.5)*S/D - 0.5, s = floor(f), w = f - s,
+// clamped to [0, S-1] with w = 0 at the clamps.
+struct Taps64 {
+  int i[4];
+  double w[4];
+};
+__device__ Taps64 composite_taps(int d, int N, int m, int pad) {
+  Taps64 t;
+  const int P = N + 2 * pad;
+  const int Cs = N - 2 * m;
+  double f = (d + 0.5) * ((double)P / (double)N) - 0.5;
+  int s = (int)floor(f);
+  double w = f - (double)s;
+  if (s < 0) { s = 0; w = 0.0; }
+  if (s >= P - 1) { s = P - 1; w = 0.0; }
+  const int s1 = min(s + 1, P - 1);
+  const int z[2] = {s - pad, s1 - pad};
+  const double wz[2] = {1.0 - w, w};
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {
+    if (z[a] < 0 || z[a] >= N || wz[a] == 0.0) {
+      t.i[2 * a] = t.i[2 * a + 1] = m;
+      t.w[2 * a] = t.w[2 * a + 1] = 0.0;
+      continue;
+    }
+    double g = (z[a] + 0.5) * ((double)Cs / (double)N) - 0.5;
+    int u = (int)floor(g);
+    double v = g - (double)u;
+    if (u < 0) { u = 0; v = 0.0; }
+    if (u >= Cs - 1) { u = Cs - 1; v = 0.0; }
+    const int u1 = min(u + 1, Cs - 1);
+    t.i[2 * a] = m + u;
+    t.i[2 * a + 1] = m + u1;
+    t.w[2 * a] = wz[a] * (1.0 - v);
+    t.w[2 * a + 1] = wz[a] * v;
+  }
+  return t;
+}
+
+// ---- warp 0: float64 parameter block -> compacted float32 coefficients ----------
+__device__ void build_coefs(Fixed& sm, const double* P, int slots, int N, int lane) {
+  float amax = 0.f;
+  for (int k = lane; k < slots; k += 32) amax = fmaxf(amax, fabsf((float)P[k * 6]));
+  amax = warp_max(amax);
+  const double tau = 1e-8 * (double)amax;  // image peak >= max amp: < 2e-7 of peak dropped
+  int base = 0;
+  for (int k0 = 0; k0 < slots; k0 += 32) {
+    const int k = k0 + lane;
+    bool live = false;
+    Coef c;
+    if (k < slots) {
+      const double* p = P + k * 6;
+      const double amp = p[0], x = p[1], y = p[2], sx = p[3], sy = p[4];
+      if (amp != 0.0 && fabs(amp) > tau) {
+        double sr, cr;
+        sincos(p[5], &sr, &cr);
+        // u = (dr cr - dc sr)/sy, v = (dr sr + dc cr)/sx ; exponent = -(u^2+v^2)/2 * log2(e)
+        const double h = 0.5 * 1.4426950408889634;
+        const double iu = 1.0 / (sy * sy), iv = 1.0 / (sx * sx);
+        c.A = (float)(-h * (sr * sr * iu + cr * cr * iv));
+        c.C = (float)(-h * (cr * cr * iu + sr * sr * iv));
+        c.B = (float)(-2.0 * h * sr * cr * (iv - iu));
+        c.amp = (float)amp;
+        const double yr = rint(y), xr = rint(x);
+        c.irf = (float)yr;
+        c.fr = (float)(y - yr);
+        c.icf = (float)xr;
+        c.fc = (float)(x - xr);
+        const double T = sqrt(2.0 * log(fabs(amp) / tau));
+        const double er = T * sqrt(sy * sy * cr * cr + sx * sx * sr * sr);
+        const double ec = T * sqrt(sy * sy * sr * sr + sx * sx * cr * cr);
+        const double lo_r = fmax(floor(y - er), 0.0), hi_r = fmin(ceil(y + er), (double)(N - 1));
+        const double lo_c = fmax(floor(x - ec), 0.0), hi_c = fmin(ceil(x + ec), (double)(N - 1));
+        live = (lo_r <= hi_r) && (lo_c <= hi_c) && isfinite(er) && isfinite(ec);
+        if (!(isfinite(er) && isfinite(ec))) {  // degenerate widths: keep, never cull
+          live = true;
+          c.r0 = 0; c.r1 = N - 1; c.c0 = 0; c.c1 = N - 1;
+        } else if (live) {
+          c.r0 = (int)lo_r; c.r1 = (int)hi_r; c.c0 = (int)lo_c; c.c1 = (int)hi_c;
+        }
+      }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, live);
+    if (live) sm.coef[base + __popc(mask & ((1u << lane) - 1u))] = c;
+    base += __popc(mask);
+  }
+  if (lane == 0) {
+    sm.nlive = base;
+    sm.delta = 2e-6f * fmaxf(1.f, amax);
+  }
+}
+
+// 4 consecutive pixels of one row, all live components (culled per strip).
+__device__ __forceinline__ void splat_row4(const Coef* __restrict__ coef, int nlive, int r,
+                                           float rf, int strip_c0, float c0f, float acc[4]) {
+  const int strip_c1 = strip_c0 + kStrip - 1;
+  for (int k = 0; k < nlive; ++k) {
+    const Coef c = coef[k];
+    if (r < c.r0 || r > c.r1 || strip_c1 < c.c0 || strip_c0 > c.c1) continue;  // warp-uniform
+    const float dr = (rf - c.irf) - c.fr;
+    const float dc = (c0f - c.icf) - c.fc;
+    const float Bq = c.B * dr;
+    const float Cq = c.C * dr * dr;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float d = dc + (float)j;
+      const float t = fmaf(fmaf(c.A, d, Bq), d, Cq);
+      acc[j] = fmaf(c.amp, ex2(t), acc[j]);
+    }
+  }
+}
+
+template <typename OutT>
+__device__ __forceinline__ void store4(OutT* row, int c0, int N, bool vec, float4 v) {
+  if (vec) {
+    if constexpr (sizeof(OutT) == 4) {
+      *reinterpret_cast<float4*>(row + c0) = v;
+    } else {
+      double2* p = reinterpret_cast<double2*>(row + c0);
+      p[0] = make_double2((double)v.x, (double)v.y);
+      p[1] = make_double2((double)v.z, (double)v.w);
+    }
+  } else {
+    const float a[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (c0 + j < N) row[c0 + j] = (OutT)a[j];
+  }
+}
+
+template <bool kSmemRaw, int NS, typename OutT>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm) jet_kernel(const Args a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Fixed& sm = *reinterpret_cast<Fixed*>(smem_raw);
+  const int N = a.size, pitch = a.pitch, slots = a.slots;
+  const int npad = (N + 3) & ~3;
+  float* tab_w = reinterpret_cast<float*>(smem_raw + sizeof(Fixed));  // [4][npad]
+  int* tab_i = reinterpret_cast<int*>(tab_w + 4 * npad);              // [4][npad]
+  float* raw;
+  if constexpr (kSmemRaw)
+    raw = reinterpret_cast<float*>(tab_i + 4 * npad);
+  else
+    raw = a.scratch + (size_t)blockIdx.x * (size_t)pitch * (size_t)N;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
+  const int strips = (N + kStrip - 1) / kStrip;
+  const int items = N * strips;
+  const bool vec = (N & 3) == 0;
+
+  if (tid == 0) {
+    mbar_init(&sm.bar[0], 1);
+    mbar_init(&sm.bar[1], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0 && (int)blockIdx.x < a.n) {
+    mbar_expect_tx(&sm.bar[0], pbytes);
+    bulk_g2s(sm.params[0], a.params + (size_t)blockIdx.x * slots * 6, pbytes, &sm.bar[0]);
+  }
+
+  int it = 0;
+  for (int img = blockIdx.x; img < a.n; img += gridDim.x, ++it) {
+    const int buf = it & 1;
+    // prefetch the next image's parameter block into the other buffer
+    if (tid == 0 && img + (int)gridDim.x < a.n) {
+      fence_proxy_async();
+      mbar_expect_tx(&sm.bar[buf ^ 1], pbytes);
+      bulk_g2s(sm.params[buf ^ 1], a.params + (size_t)(img + gridDim.x) * slots * 6, pbytes,
+               &sm.bar[buf ^ 1]);
+    }
+    mbar_wait(&sm.bar[buf], (it >> 1) & 1);
+    const double* P = sm.params[buf];
+    const int zpad = a.zoom_pad[img];
+    const bool zoom = zpad >= 0;
+    const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
+
+    if (warp == 0) build_coefs(sm, P, slots, N, lane);
+    __syncthreads();
+    const int nlive = sm.nlive;
+    const float thr = (float)kEdgeThr, delta = sm.delta;
+
+    // ---------------- phase 1: splat ------------------------------------------
+    int my_margin = N;                  // zoom branch: min border distance of px > thr
+    unsigned long long my_best = 0ull;  // else: (value bits << 32) | ~pixel index
+    for (int item = warp; item < items; item += kWarps) {
+      const int r = item / strips, s = item - r * strips;
+      const int c0 = s * kStrip + 4 * lane;
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      splat_row4(sm.coef, nlive, r, (float)r, s * kStrip, (float)c0, acc);
+      if (c0 < N) {
+        *reinterpret_cast<float4*>(raw + (size_t)r * pitch + c0) =
+            make_float4(acc[0], acc[1], acc[2], acc[3]);
+        if (zoom) {
+          const float top = fmaxf(fmaxf(acc[0], acc[1]), fmaxf(acc[2], acc[3]));
+          if (top > thr - delta) {
+            const int dr = min(r, N - 1 - r);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int c = c0 + j;
+              const int d = min(dr, min(c, N - 1 - c));
+              if (c < N && d < my_margin && acc[j] > thr - delta) {
+                bool above = acc[j] > thr;
+                if (acc[j] < thr + delta) above = eval64(P, slots, r, c) > kEdgeThr;
+                if (above) my_margin = d;
+              }
+            }
+          }
+        } else if (normalize) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = c0 + j;
+            if (c < N) {
+              const unsigned long long key =
+                  ((unsigned long long)__float_as_uint(fmaxf(acc[j], 0.f)) << 32) |
+                  (unsigned)(~(unsigned)(r * N + c));
+              my_best = key > my_best ? key : my_best;
+            }
+          }
+        }
+      }
+    }
+
+    double peak = 1.0;
+    int margin = 0;
+    OutT* out = reinterpret_cast<OutT*>(a.out) + (size_t)img * N * N;
+
+    if (!zoom) {
+      // ------------- plain branch: (normalise and) write the raw image ----------
+      if (normalize) {
+        my_best = warp_max_u64(my_best);
+        if (lane == 0) sm.red_u[warp] = my_best;
+        __syncthreads();
+        if (warp == 0) {
+          unsigned long long b = lane < kWarps ? sm.red_u[lane] : 0ull;
+          b = warp_max_u64(b);
+          if (lane == 0) {
+            const unsigned idx = ~(unsigned)(b & 0xffffffffull);
+            sm.peak = eval64(P, slots, (int)(idx / (unsigned)N), (int)(idx % (unsigned)N));
+          }
+        }
+        __syncthreads();
+        peak = sm.peak;
+      } else {
+        __syncthreads();
+      }
+      const float inv = normalize ? (float)(1.0 / peak) : 1.f;
+      const int q = npad >> 2;
+      for (int e = tid; e < N * q; e += kThreads) {
+        const int r = e / q, c0 = (e - r * q) << 2;
+        float4 v = *reinterpret_cast<const float4*>(raw + (size_t)r * pitch + c0);
+        v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+        store4<OutT>(out + (size_t)r * N, c0, N, vec, v);
+      }
+    } else {
+      // ------------- zoom branch ------------------------------------------------
+      my_margin = warp_min(my_margin);
+      if (lane == 0) sm.red_i[warp] = my_margin;
+      __syncthreads();
+      if (warp == 0) {
+        int m = lane < kWarps ? sm.red_i[lane] : N;
+        m = warp_min(m);
+        if (lane == 0) sm.margin = (m >= N) ? 0 : m;  // empty mask -> idx 0 (argmax of zeros)
+      }
+      __syncthreads();
+      margin = sm.margin;
+      for (int d = tid; d < npad; d += kThreads) {
+        if (d < N) {
+          const Taps64 t = composite_taps(d, N, margin, zpad);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            tab_w[k * npad + d] = (float)t.w[k];
+            tab_i[k * npad + d] = t.i[k];
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            tab_w[k * npad + d] = 0.f;
+            tab_i[k * npad + d] = margin;
+          }
+        }
+      }
+      __syncthreads();
+
+      // H pass, in place: row r' of raw becomes row r' of T (all N columns).
+      for (int r = margin + warp; r < N - margin; r += kWarps) {
+        float* row = raw + (size_t)r * pitch;
+        float4 res[NS];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+          const int c0 = s * kStrip + 4 * lane;
+          res[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (c0 < N) {
+            float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float4 w = *reinterpret_cast<const float4*>(tab_w + k * npad + c0);
+              const int4 i = *reinterpret_cast<const int4*>(tab_i + k * npad + c0);
+              o[0] = fmaf(w.x, row[i.x], o[0]);
+              o[1] = fmaf(w.y, row[i.y], o[1]);
+              o[2] = fmaf(w.z, row[i.z], o[2]);
+              o[3] = fmaf(w.w, row[i.w], o[3]);
+            }
+            res[s] = make_float4(o[0], o[1], o[2], o[3]);
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+          const int c0 = s * kStrip + 4 * lane;
+          if (c0 < N) *reinterpret_cast<float4*>(row + c0) = res[s];
+        }
+      }
+      __syncthreads();
+
+      // V pass A: maximum (and where) of the resampled image.
+      float inv = 1.f;
+      if (normalize) {
+        my_best = 0ull;
+        for (int item = warp; item < items; item += kWarps) {
+          const int r = item / strips, s = item - r * strips;
+          const int c0 = s * kStrip + 4 * lane;
+          const float w0 = tab_w[r], w1 = tab_w[npad + r], w2 = tab_w[2 * npad + r],
+                      w3 = tab_w[3 * npad + r];
+          if (c0 >= N || (w0 == 0.f && w1 == 0.f && w2 == 0.f && w3 == 0.f)) continue;
+          const float4 t0 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[r] * pitch + c0);
+          const float4 t1 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[npad + r] * pitch + c0);
+          const float4 t2 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[2 * npad + r] * pitch + c0);
+          const float4 t3 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[3 * npad + r] * pitch + c0);
+          const float v[4] = {fmaf(w3, t3.x, fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x))),
+                              fmaf(w3, t3.y, fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y))),
+                              fmaf(w3, t3.z, fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z))),
+                              fmaf(w3, t3.w, fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w)))};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = c0 + j;
+            if (c < N) {
+              const unsigned long long key =
+                  ((unsigned long long)__float_as_uint(fmaxf(v[j], 0.f)) << 32) |
+                  (unsigned)(~(unsigned)(r * N + c));
+              my_best = key > my_best ? key : my_best;
+            }
+          }
+        }
+        my_best = warp_max_u64(my_best);
+        if (lane == 0) sm.red_u[warp] = my_best;
+        __syncthreads();
+        if (warp == 0) {
+          unsigned long long b = lane < kWarps ? sm.red_u[lane] : 0ull;
+          b = warp_max_u64(b);
+          // float64 value of the arg-max pixel: 4x4 raw pixels, float64 weights
+          const unsigned idx = ~(unsigned)(b & 0xffffffffull);
+          const int pr = (int)(idx / (unsigned)N), pc = (int)(idx % (unsigned)N);
+          const Taps64 tr = composite_taps(pr, N, margin, zpad);
+          const Taps64 tc = composite_taps(pc, N, margin, zpad);
+          if (lane < 16) {
+            const int i = lane >> 2, j = lane & 3;
+            const double w = tr.w[i] * tc.w[j];
+            sm.pix64[lane] = (w != 0.0) ? eval64(P, slots, tr.i[i], tc.i[j]) : 0.0;
+          }
+          __syncwarp();
+          if (lane == 0) {
+            double acc = 0.0;
+            for (int i = 0; i < 4; ++i) {
+              double h = 0.0;
+              for (int j = 0; j < 4; ++j) h += tc.w[j] * sm.pix64[i * 4 + j];
+              acc += tr.w[i] * h;
+            }
+            sm.peak = acc;
+          }
+        }
+        __syncthreads();
+        peak = sm.peak;
+        inv = (float)(1.0 / peak);
+      }
+
+      // V pass B: recompute, scale, write every output pixel once.
+      for (int item = warp; item < items; item += kWarps) {
+        const int r = item / strips, s = item - r * strips;
+        const int c0 = s * kStrip + 4 * lane;
+        if (c0 >= N) continue;
+        const float w0 = tab_w[r] * inv, w1 = tab_w[npad + r] * inv, w2 = tab_w[2 * npad + r] * inv,
+                    w3 = tab_w[3 * npad + r] * inv;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!(w0 == 0.f && w1 == 0.f && w2 == 0.f && w3 == 0.f)) {
+          const float4 t0 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[r] * pitch + c0);
+          const float4 t1 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[npad + r] * pitch + c0);
+          const float4 t2 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[2 * npad + r] * pitch + c0);
+          const float4 t3 = *reinterpret_cast<const float4*>(raw + (size_t)tab_i[3 * npad + r] * pitch + c0);
+          v.x = fmaf(w3, t3.x, fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x)));
+          v.y = fmaf(w3, t3.y, fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y)));
+          v.z = fmaf(w3, t3.z, fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z)));
+          v.w = fmaf(w3, t3.w, fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w)));
+        }
+        store4<OutT>(out + (size_t)r * N, c0, N, vec, v);
+      }
+    }
+    if (tid == 0) {
+      a.margin[img] = margin;
+      a.peak[img] = peak;
+    }
+    __syncthreads();  // raw / tab / coef / params[buf] are reused by the next image
+  }
+}
+
+// ------------------------------------------------------------------ host side
+struct Plan {
+  bool smem_raw;
+  int ns;
+  size_t smem_bytes;
+  int grid_cap;  // CTAs that can be resident
+  int pitch;
+};
+
+static size_t fixed_bytes(int size) {
+  const int npad = (size + 3) & ~3;
+  return sizeof(Fixed) + (size_t)npad * 32;
+}
+
+static int make_plan(int size, Plan* p) {
+  int dev = 0, max_optin = 0;
+  RSB_CUDA(cudaGetDevice(&dev));
+  RSB_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  p->pitch = (size + 3) & ~3;
+  const size_t raw_bytes = (size_t)p->pitch * size * 4;
+  const size_t fx = fixed_bytes(size);
+  p->smem_raw = fx + raw_bytes <= (size_t)max_optin;
+  p->smem_bytes = fx + (p->smem_raw ? raw_bytes : 0);
+  const int strips = (size + kStrip - 1) / kStrip;
+  p->ns = strips <= 1 ? 1 : strips <= 2 ? 2 : strips <= 4 ? 4 : 8;
+  // per-SM residency: threads (2048/512 = 4, capped by launch bounds) and shared memory
+  int per_sm = kCtasPerSm;
+  const size_t sm_total = 228 * 1024;
+  const int by_smem = (int)(sm_total / (p->smem_bytes + 1024));
+  if (by_smem < per_sm) per_sm = by_smem < 1 ? 1 : by_smem;
+  p->grid_cap = sm_count() * per_sm;
+  return 0;
+}
+
+template <bool S, int NS, typename T>
+static int launch_one(const Args& a, const Plan& p, int grid, cudaStream_t st) {
+  auto k = jet_kernel<S, NS, T>;
+  RSB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bytes));
+  k<<<grid, kThreads, p.smem_bytes, st>>>(a);
+  RSB_LAUNCHED();
+  return 0;
+}
+
+template <bool S, typename T>
+static int launch_ns(const Args& a, const Plan& p, int grid, cudaStream_t st) {
+  switch (p.ns) {
+    case 1: return launch_one<S, 1, T>(a, p, grid, st);
+    case 2: return launch_one<S, 2, T>(a, p, grid, st);
+    case 4: return launch_one<S, 4, T>(a, p, grid, st);
+    default: return launch_one<S, 8, T>(a, p, grid, st);
+  }
+}
+
+static int launch(const Args& a, const Plan& p, int grid, cudaStream_t st) {
+  const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
+  if (p.smem_raw) return f64 ? launch_ns<true, double>(a, p, grid, st) : launch_ns<true, float>(a, p, grid, st);
+  return f64 ? launch_ns<false, double>(a, p, grid, st) : launch_ns<false, float>(a, p, grid, st);
+}
+
+// ---------------------------------------------------------------- plane kernel
+// training_type == "gauss": slot planes after zoom_on_source, divided by the peak.
+// Each output pixel is the bilinear blend of <= 4 analytic Gaussian samples.
+struct PlaneArgs {
+  const double* params;
+  const int32_t* zoom_pad;
+  const int32_t* margin;
+  const double* peak;
+  int n, slots, size;
+  unsigned flags;
+  void* out;
+};
+
+template <typename OutT>
+__global__ void __launch_bounds__(256) planes_kernel(const PlaneArgs a) {
+  // grid: (row blocks, slot, image)
+  const int img = blockIdx.z, k = blockIdx.y, N = a.size;
+  const double* p = a.params + ((size_t)img * a.slots + k) * 6;
+  OutT* out = reinterpret_cast<OutT*>(a.out) + ((size_t)img * a.slots + k) * N * N;
+  const double amp = p[0];
+  const bool zoom = a.zoom_pad[img] >= 0;
+  const int m = a.margin[img];
+  const float inv = (a.flags & RSB_JET_NORMALIZE) ? (float)(1.0 / a.peak[img]) : 1.f;
+  float A = 0.f, B = 0.f, C = 0.f, xc = 0.f, yc = 0.f, fxc = 0.f, fyc = 0.f;
+  if (amp != 0.0) {
+    double sr, cr;
+    sincos(p[5], &sr, &cr);
+    const double h = 0.5 * 1.4426950408889634;
+    const double iu = 1.0 / (p[4] * p[4]), iv = 1.0 / (p[3] * p[3]);
+    A = (float)(-h * (sr * sr * iu + cr * cr * iv));
+    C = (float)(-h * (cr * cr * iu + sr * sr * iv));
+    B = (float)(-2.0 * h * sr * cr * (iv - iu));
+    xc = (float)rint(p[1]); fxc = (float)(p[1] - rint(p[1]));
+    yc = (float)rint(p[2]); fyc = (float)(p[2] - rint(p[2]));
+  }
+  const float ampf = (float)amp * inv;
+  const int Cs = N - 2 * m;
+  const double sc = (double)Cs / (double)N;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < N * N; e += gridDim.x * blockDim.x) {
+    const int r = e / N, c = e - r * N;
+    float v = 0.f;
+    if (amp != 0.0) {
+      int ri[2] = {r, r}, ci[2] = {c, c};
+      float wr = 0.f, wc = 0.f;
+      if (zoom) {
+        double g = (r + 0.5) * sc - 0.5;
+        int u = (int)floor(g);
+        double w = g - u;
+        if (u < 0) { u = 0; w = 0; }
+        if (u >= Cs - 1) { u = Cs - 1; w = 0; }
+        ri[0] = m + u; ri[1] = m + min(u + 1, Cs - 1); wr = (float)w;
+        g = (c + 0.5) * sc - 0.5;
+        u = (int)floor(g);
+        w = g - u;
+        if (u < 0) { u = 0; w = 0; }
+        if (u >= Cs - 1) { u = Cs - 1; w = 0; }
+        ci[0] = m + u; ci[1] = m + min(u + 1, Cs - 1); wc = (float)w;
+      }
+      float s[2][2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const float dr = ((float)ri[i] - yc) - fyc, dc = ((float)ci[j] - xc) - fxc;
+          s[i][j] = ex2(fmaf(fmaf(A, dc, B * dr), dc, C * dr * dr));
+        }
+      const float top = fmaf(wc, s[0][1] - s[0][0], s[0][0]);
+      const float bot = fmaf(wc, s[1][1] - s[1][0], s[1][0]);
+      v = ampf * fmaf(wr, bot - top, top);
+    }
+    out[e] = (OutT)v;
+  }
+}
+
+}  // namespace jet
+}  // namespace rsb
+
+using namespace rsb;
+using namespace rsb::jet;
+
+static int check_common(const char* fn, int n, int slots, int size) {
+  RSB_ARG(n >= 0, "%s: n must be >= 0 (got %d)", fn, n);
+  RSB_ARG(slots >= 1 && slots <= kMaxSlots, "%s: slots must be in [1, %d] (got %d)", fn, kMaxSlots, slots);
+  RSB_ARG(size >= 2 && size <= 1024, "%s: size must be in [2, 1024] (got %d)", fn, size);
+  return 0;
+}
+
+extern "C" {
+
+int rsb_jet_workspace_bytes(int n, int slots, int size, size_t* bytes) {
+  RSB_ARG(bytes != nullptr, "rsb_jet_workspace_bytes: bytes is NULL");
+  if (int e = check_common("rsb_jet_workspace_bytes", n, slots, size)) return e;
+  Plan p;
+  if (int e = make_plan(size, &p)) return e;
+  if (p.smem_raw) {
+    *bytes = 0;
+  } else {
+    const int grid = n < p.grid_cap ? (n > 0 ? n : 1) : p.grid_cap;
+    *bytes = (size_t)grid * p.pitch * size * sizeof(float);
+  }
+  return 0;
+}
+
+int rsb_jet_render(const double* params, const int32_t* zoom_pad, int n, int slots, int size,
+                   unsigned flags, void* out_img, int32_t* out_margin, double* out_peak,
+                   void* workspace, size_t workspace_bytes, void* stream) {
+  if (int e = check_common("rsb_jet_render", n, slots, size)) return e;
+  if (n == 0) return 0;
+  RSB_ARG(params && zoom_pad && out_img && out_margin && out_peak, "rsb_jet_render: NULL buffer");
+  RSB_ARG(((uintptr_t)params & 15) == 0, "rsb_jet_render: params must be 16-byte aligned");
+  Plan p;
+  if (int e = make_plan(size, &p)) return e;
+  const int grid = n < p.grid_cap ? n : p.grid_cap;
+  if (!p.smem_raw) {
+    const size_t need = (size_t)grid * p.pitch * size * sizeof(float);
+    RSB_ARG(workspace != nullptr && workspace_bytes >= need,
+            "rsb_jet_render: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+  }
+  Args a;
+  a.params = params; a.zoom_pad = zoom_pad; a.n = n; a.slots = slots; a.size = size;
+  a.flags = flags; a.out = out_img; a.margin = out_margin; a.peak = out_peak;
+  a.scratch = (float*)workspace; a.pitch = p.pitch;
+  return launch(a, p, grid, (cudaStream_t)stream);
+}
+
+int rsb_jet_planes(const double* params, const int32_t* zoom_pad, const int32_t* margin,
+                   const double* peak, int n, int slots, int size, unsigned flags, void* out,
+                   void* stream) {
+  if (int e = check_common("rsb_jet_planes", n, slots, size)) return e;
+  if (n == 0) return 0;
+  RSB_ARG(params && zoom_pad && margin && peak && out, "rsb_jet_planes: NULL buffer");
+  PlaneArgs a{params, zoom_pad, margin, peak, n, slots, size, flags, out};
+  int bx = (size * size + 255) / 256;
+  if (bx > 64) bx = 64;
+  // grid.z is limited to 65535 images per launch
+  for (int i0 = 0; i0 < n; i0 += 65535) {
+    const int cnt = (n - i0) < 65535 ? (n - i0) : 65535;
+    PlaneArgs b = a;
+    b.params += (size_t)i0 * slots * 6;
+    b.zoom_pad += i0; b.margin += i0; b.peak += i0;
+    const size_t esz = (flags & RSB_JET_OUT_F64) ? 8 : 4;
+    b.out = (char*)out + (size_t)i0 * slots * size * size * esz;
+    dim3 grid(bx, slots, cnt);
+    if (flags & RSB_JET_OUT_F64)
+      planes_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>(b);
+    else
+      planes_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(b);
+    RSB_LAUNCHED();
+  }
+  return 0;
+}
+
+
+// ---- host-buffer convenience: chunked, 3 streams, copy/compute overlap ------------
+namespace {
+struct HostCtx {
+  static constexpr int kLanes = 3;
+  cudaStream_t st[kLanes] = {nullptr, nullptr, nullptr};
+  void* params[kLanes] = {nullptr, nullptr, nullptr};
+  void* pad[kLanes] = {nullptr, nullptr, nullptr};
+  void* out[kLanes] = {nullptr, nullptr, nullptr};
+  void* margin[kLanes] = {nullptr, nullptr, nullptr};
+  void* peak[kLanes] = {nullptr, nullptr, nullptr};
+  void* work[kLanes] = {nullptr, nullptr, nullptr};
+  size_t cap_params = 0, cap_out = 0, cap_n = 0, cap_work = 0;
+};
+std::mutex g_host_mu;
+HostCtx g_host_ctx[64];
+
+int grow(void** p, size_t bytes) {
+  if (*p) RSB_CUDA(cudaFree(*p));
+  *p = nullptr;
+  RSB_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+  return 0;
+}
+}  // namespace
+
+int rsb_jet_render_host(const double* params, const int32_t* zoom_pad, int n, int slots, int size,
+                        unsigned flags, void* out_img, int32_t* out_margin, double* out_peak) {
+  if (int e = check_common("rsb_jet_render_host", n, slots, size)) return e;
+  if (n == 0) return 0;
+  RSB_ARG(params && zoom_pad && out_img && out_margin && out_peak, "rsb_jet_render_host: NULL buffer");
+  int dev = 0;
+  RSB_CUDA(cudaGetDevice(&dev));
+  RSB_ARG(dev >= 0 && dev < 64, "rsb_jet_render_host: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_host_mu);
+  HostCtx& cx = g_host_ctx[dev];
+  const size_t esz = (flags & RSB_JET_OUT_F64) ? 8 : 4;
+  const size_t img_bytes = (size_t)size * size * esz;
+  const size_t par_bytes = (size_t)slots * 6 * sizeof(double);
+  size_t chunk = ((size_t)96 << 20) / img_bytes;
+  if (chunk < 320) chunk = 320;
+  if (chunk > 16384) chunk = 16384;
+  if (chunk > (size_t)n) chunk = (size_t)n;
+  size_t work_bytes = 0;
+  if (int e = rsb_jet_workspace_bytes((int)chunk, slots, size, &work_bytes)) return e;
+  for (int l = 0; l < HostCtx::kLanes; ++l)
+    if (!cx.st[l]) RSB_CUDA(cudaStreamCreateWithFlags(&cx.st[l], cudaStreamNonBlocking));
+  if (cx.cap_params < chunk * par_bytes) {
+    for (int l = 0; l < HostCtx::kLanes; ++l)
+      if (int e = grow(&cx.params[l], chunk * par_bytes)) return e;
+    cx.cap_params = chunk * par_bytes;
+  }
+  if (cx.cap_out < chunk * img_bytes) {
+    for (int l = 0; l < HostCtx::kLanes; ++l)
+      if (int e = grow(&cx.out[l], chunk * img_bytes)) return e;
+    cx.cap_out = chunk * img_bytes;
+  }
+  if (cx.cap_n < chunk) {
+    for (int l = 0; l < HostCtx::kLanes; ++l) {
+      if (int e = grow(&cx.pad[l], chunk * 4)) return e;
+      if (int e = grow(&cx.margin[l], chunk * 4)) return e;
+      if (int e = grow(&cx.peak[l], chunk * 8)) return e;
+    }
+    cx.cap_n = chunk;
+  }
+  if (cx.cap_work < work_bytes) {
+    for (int l = 0; l < HostCtx::kLanes; ++l)
+      if (int e = grow(&cx.work[l], work_bytes)) return e;
+    cx.cap_work = work_bytes;
+  }
+  int lane = 0;
+  for (size_t i0 = 0; i0 < (size_t)n; i0 += chunk, lane = (lane + 1) % HostCtx::kLanes) {
+    const size_t cnt = ((size_t)n - i0) < chunk ? ((size_t)n - i0) : chunk;
+    cudaStream_t st = cx.st[lane];
+    RSB_CUDA(cudaMemcpyAsync(cx.params[lane], params + i0 * slots * 6, cnt * par_bytes,
+                             cudaMemcpyHostToDevice, st));
+    RSB_CUDA(cudaMemcpyAsync(cx.pad[lane], zoom_pad + i0, cnt * 4, cudaMemcpyHostToDevice, st));
+    if (int e = rsb_jet_render((const double*)cx.params[lane], (const int32_t*)cx.pad[lane], (int)cnt,
+                               slots, size, flags, cx.out[lane], (int32_t*)cx.margin[lane],
+                               (double*)cx.peak[lane], cx.work[lane], cx.cap_work, (void*)st))
+      return e;
+    RSB_CUDA(cudaMemcpyAsync((char*)out_img + i0 * img_bytes, cx.out[lane], cnt * img_bytes,
+                             cudaMemcpyDeviceToHost, st));
+    RSB_CUDA(cudaMemcpyAsync(out_margin + i0, cx.margin[lane], cnt * 4, cudaMemcpyDeviceToHost, st));
+    RSB_CUDA(cudaMemcpyAsync(out_peak + i0, cx.peak[lane], cnt * 8, cudaMemcpyDeviceToHost, st));
+  }
+  for (int l = 0; l < HostCtx::kLanes; ++l) RSB_CUDA(cudaStreamSynchronize(cx.st[l]));
+  return 0;
+}
+
+}  // extern "C"

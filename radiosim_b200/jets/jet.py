@@ -1,0 +1,114 @@
+"""Drop-in ``create_jet`` / ``component_from_list`` / ``apply_train_type``.
+
+Same signatures, return shapes and dtypes as the reference's
+``src/radiosim/jets/jet.py:14-261``; the pixel work runs in ``librsb200.so``
+(``rsb_jet_render`` / ``rsb_jet_planes``), the RNG chain in :mod:`.packer`.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .. import _lib as L
+from .packer import JetBatch, pack_jets, source_lists
+
+__all__ = ["apply_train_type", "component_from_list", "create_jet", "render_batch"]
+
+
+def render_batch(batch: JetBatch, normalize: bool, planes: bool = False, f64: bool = True):
+    """Render a packed batch on the current device through the host-buffer C ABI.
+
+    Returns ``(images[n, N, N], margin[n] int32, peak[n] float64, planes or None)``.
+    """
+    L.require_device()
+    n, size, slots = batch.n, batch.size, batch.slots
+    flags = (L.JET_NORMALIZE if normalize else 0) | (L.JET_OUT_F64 if f64 else 0)
+    dt = np.float64 if f64 else np.float32
+    img = L.pinned_empty((n, size, size), dt)
+    margin = L.pinned_empty((n,), np.int32)
+    peak = L.pinned_empty((n,), np.float64)
+    p = np.ascontiguousarray(batch.params, dtype=np.float64)
+    zp = np.ascontiguousarray(batch.zoom_pad, dtype=np.int32)
+    if n:
+        L.check(
+            L.lib().rsb_jet_render_host(
+                p.ctypes.data, zp.ctypes.data, n, slots, size, flags,
+                img.ctypes.data, margin.ctypes.data, peak.ctypes.data,
+            ),
+            "rsb_jet_render_host",
+        )
+    pl = None
+    if planes:
+        pl = np.empty((n, slots, size, size), dtype=dt)
+        step = max(1, (256 << 20) // (slots * size * size * pl.itemsize))
+        for i0 in range(0, n, step):
+            i1 = min(n, i0 + step)
+            d_p = L.dev_from(p[i0:i1])
+            d_z = L.dev_from(zp[i0:i1])
+            d_m = L.dev_from(np.asarray(margin[i0:i1]))
+            d_k = L.dev_from(np.asarray(peak[i0:i1]))
+            d_o = L.DeviceBuffer(pl[i0:i1].nbytes)
+            L.check(
+                L.lib().rsb_jet_planes(
+                    d_p.ptr, d_z.ptr, d_m.ptr, d_k.ptr, i1 - i0, slots, size, flags, d_o.ptr, None
+                ),
+                "rsb_jet_planes",
+            )
+            pl[i0:i1] = d_o.download(pl[i0:i1].shape, dt)
+    return img, np.asarray(margin), np.asarray(peak), pl
+
+
+def apply_train_type(train_type, jet_img, jet_comp, source_list):
+    """``src/radiosim/jets/jet.py:200-231``."""
+    if train_type == "list":
+        return source_list
+    if train_type == "gauss":
+        size = jet_comp.shape[-1]
+        tail = np.full((1, size, size), np.nan)
+        tail[0, : source_list.shape[0], : source_list.shape[1]] = source_list
+        return np.concatenate((jet_comp, tail))
+    if train_type == "clean":
+        return jet_img[None]
+    raise UnboundLocalError(f"unknown training type {train_type!r}")
+
+
+def create_jet(grid, conf):
+    """Drop-in for ``radiosim.jets.create_jet`` (``jets/jet.py:14-197``).
+
+    ``grid`` is only inspected for its shape (as in the reference, ``:46-53``);
+    ``conf`` needs ``conf.jet.num_jet_components / scaling / training_type``.
+    """
+    shape = tuple(grid.shape)
+    n = 1 if len(shape) == 3 else shape[0]
+    size = shape[-1]
+    scaling = conf.jet.scaling
+    ttype = conf.jet.training_type
+    batch = pack_jets(n, size, conf.jet.num_jet_components, scaling)
+    normalize = scaling == "normalize"
+    img, margin, peak, planes = render_batch(batch, normalize, planes=(ttype == "gauss"))
+    slist = source_lists(batch, margin, peak, normalize)
+    jets = np.array(img)[:, None, :, :]
+    if ttype == "list":
+        targets = slist
+    elif ttype == "clean":
+        targets = jets.copy()
+    elif ttype == "gauss":
+        targets = np.empty((n, batch.slots + 2, size, size))
+        targets[:, : batch.slots] = planes
+        targets[:, batch.slots] = 1 - jets[:, 0]
+        targets[:, batch.slots + 1] = np.nan
+        targets[:, batch.slots + 1, : batch.slots, :8] = slist
+    else:
+        raise UnboundLocalError(f"unknown training type {ttype!r}")
+    return jets, targets
+
+
+def component_from_list(size, amp, x, y, sx, sy, rotation):
+    """``src/radiosim/jets/jet.py:234-261``: one float64 plane per slot (zeros for
+    ``amp == 0``), rendered on the device."""
+    from ..utils.gauss import gaussian_planes
+
+    p = np.stack([np.asarray(v, dtype=np.float64) for v in (amp, x, y, sx, sy, rotation)], axis=-1)
+    return list(gaussian_planes(p, size))
