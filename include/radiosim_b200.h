@@ -113,6 +113,29 @@ int rsb_jet_render_host(const double* params_host, const int32_t* zoom_pad_host,
                         int slots, int size, unsigned flags, void* out_img_host,
                         int32_t* out_margin_host, double* out_peak_host);
 
+/* rsb_jet_render without any allocation, for hosts that cannot call cudaMalloc once
+ * they are running: a plugin inside a process whose framework has already reserved the
+ * device for its own memory pool, or a service with a device-memory budget fixed at
+ * start-up.  (No counterpart in the reference -- it exists only because of this
+ * library's scratch requirement.)
+ *
+ * Same arguments, results and error convention as rsb_jet_render, minus the workspace:
+ * for images too large for shared memory the per-CTA raw-image slots come from a 32 MiB
+ * array compiled into the library.  That array occupies 32 MiB on every GPU that loads
+ * librsb200.so, until the process exits.
+ *  - limit: size <= 512 (larger sizes return an argument error; use rsb_jet_render).
+ *    At 256x256 the array holds 128 slots, at 512x512 32, so fewer CTAs are resident
+ *    than with a caller workspace; the images are identical.
+ *  - the first call on each device looks up the array's device address (a one-time
+ *    set-up, no allocation); make that first call before starting any stream capture.
+ *  - all calls on a device share the one array: two calls whose kernels can overlap on
+ *    the GPU (different streams, no ordering between them) race on it.  Calls on one
+ *    stream, or otherwise ordered, are safe.  Nothing in it needs clearing between calls.
+ *  - calls no cudaMalloc/cudaFree and no allocating library routine. */
+int rsb_jet_render_static(const double* params_dev, const int32_t* zoom_pad_dev, int n,
+                          int slots, int size, unsigned flags, void* out_img_dev,
+                          int32_t* out_margin_dev, double* out_peak_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

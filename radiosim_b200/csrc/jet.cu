@@ -796,4 +796,71 @@ int rsb_jet_render_host(const double* params, const int32_t* zoom_pad, int n, in
   return 0;
 }
 
+
+// ---- rsb_jet_render_static: the same renderer for callers that must not allocate ----
+// Who needs it: a host that hands this library a fixed device-memory budget at start-up
+// and forbids any later cudaMalloc -- e.g. a data-loader plugin living inside a training
+// process whose framework owns (and has already reserved) the whole device through its own
+// caching allocator, or a service whose memory is accounted per component.  For such a
+// caller rsb_jet_render's `workspace_dev` is a problem when the image does not fit in
+// shared memory (size >= ~236): it would have to carve the scratch out of somebody else's
+// pool.  Here the raw-image slots live in the library image itself instead.
+//
+// The array below is reserved on EVERY GPU that loads librsb200.so, from load until the
+// process exits, whether or not this entry point is ever called.
+constexpr size_t kStaticScratchBytes = (size_t)32 << 20;  // 32 MiB
+constexpr int kStaticMaxSize = 512;                        // largest image side served
+static __device__ __align__(256) float g_jet_static_scratch[kStaticScratchBytes / sizeof(float)];
+
+namespace {
+std::mutex g_static_mu;
+float* g_static_ptr[64] = {};  // per device: device address of g_jet_static_scratch
+}  // namespace
+
+int rsb_jet_render_static(const double* params, const int32_t* zoom_pad, int n, int slots, int size,
+                          unsigned flags, void* out_img, int32_t* out_margin, double* out_peak,
+                          void* stream) {
+  if (int e = check_common("rsb_jet_render_static", n, slots, size)) return e;
+  RSB_ARG(size <= kStaticMaxSize,
+          "rsb_jet_render_static: size %d exceeds the built-in scratch limit of %d "
+          "(use rsb_jet_render with a caller-provided workspace)", size, kStaticMaxSize);
+  if (n == 0) return 0;
+  RSB_ARG(params && zoom_pad && out_img && out_margin && out_peak, "rsb_jet_render_static: NULL buffer");
+  RSB_ARG(((uintptr_t)params & 15) == 0, "rsb_jet_render_static: params must be 16-byte aligned");
+  int dev = 0;
+  RSB_CUDA(cudaGetDevice(&dev));
+  RSB_ARG(dev >= 0 && dev < 64, "rsb_jet_render_static: device index %d out of range", dev);
+  float* scratch = nullptr;
+  {
+    // One-time set-up per device, done by the first call on that device (which is why
+    // that call must not happen while a stream is being captured).  In host code the
+    // name g_jet_static_scratch is only a stand-in; the kernel needs the device address.
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+      float* ptr = nullptr;
+      RSB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_jet_static_scratch));
+      RSB_ARG(ptr != nullptr, "rsb_jet_render_static: no device address for the scratch array");
+      g_static_ptr[dev] = ptr;
+    }
+    scratch = g_static_ptr[dev];
+  }
+  Plan p;
+  if (int e = make_plan(size, &p)) return e;
+  int grid = n < p.grid_cap ? n : p.grid_cap;
+  if (!p.smem_raw) {
+    const size_t slot = (size_t)p.pitch * size * sizeof(float);
+    const int fit = (int)(kStaticScratchBytes / slot);
+    RSB_ARG(fit >= 1, "rsb_jet_render_static: one %dx%d image does not fit the %zu-byte scratch",
+            size, size, kStaticScratchBytes);
+    if (grid > fit) grid = fit;  // fewer resident CTAs, same results (one slot per CTA)
+  }
+  // Nothing has to start at zero: every raw pixel of a slot is written (phase 1) before
+  // anything reads it, so whatever the previous call left behind is never observed.
+  Args a;
+  a.params = params; a.zoom_pad = zoom_pad; a.n = n; a.slots = slots; a.size = size;
+  a.flags = flags; a.out = out_img; a.margin = out_margin; a.peak = out_peak;
+  a.scratch = scratch; a.pitch = p.pitch;
+  return launch(a, p, grid, (cudaStream_t)stream);
+}
+
 }  // extern "C"
