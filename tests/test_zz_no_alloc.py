@@ -4,7 +4,7 @@ Some hosts of this library cannot call cudaMalloc once they are running -- a plu
 inside a process whose framework has already claimed the device for its own pool, or
 a service whose device-memory budget is fixed at start-up.  For them the scratch that
 ``rsb_jet_render`` takes from the caller (needed when the image is too large for
-shared memory, e.g. 256x256) is replaced by a 32 MiB array built into the library.
+shared memory, e.g. 384x384) is replaced by a 32 MiB array built into the library.
 
 The test drives both entry points through the C ABI on the same inputs, twice in a
 row with different batches (the shared array keeps the first call's contents, which
@@ -20,7 +20,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-SIZE = 256   # does not fit in shared memory -> both entry points use global scratch
+SIZE = 384   # too large for shared memory -> both entry points use global scratch
 SLOTS = 19
 
 
@@ -53,8 +53,8 @@ def test_static_scratch_entry_matches_workspace_entry():
 
     L.require_device()
     assert hasattr(L.lib(), "rsb_jet_render_static")
-    # more images than the 128 slots the built-in array offers at 256x256
-    for call, (seed, n) in enumerate([(101, 300), (202, 170)]):
+    # more images than the 56 slots the built-in array offers at 384x384
+    for call, (seed, n) in enumerate([(101, 150), (202, 90)]):
         np.random.seed(seed)
         b = pack_jets(n, SIZE, (3, 10), "normalize")
         assert (b.zoom_pad >= 0).any() and (b.zoom_pad < 0).any()
