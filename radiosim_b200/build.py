@@ -20,7 +20,7 @@ FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2,-Wall",
-    "--ptxas-options=-v",
+    "--ptxas-options=-v", *os.environ.get("RSB_NVCC_EXTRA", "").split(),
 ]
 
 

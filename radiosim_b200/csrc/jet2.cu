@@ -1,19 +1,25 @@
 // On-chip jet renderer: the raw image never leaves shared memory.
 //
 // One image per thread-block CLUSTER.  kCluster == 1: the whole raw image sits in one
-// CTA's shared memory (size <= ~224).  kCluster == 2: the image is split into two row
+// CTA's shared memory (size <= 128).  kCluster == 2: the image is split into two row
 // bands, one per CTA of a 2-CTA cluster (size 256: 129 x 256 floats = 132 KB each);
 // the composite zoom operator is centre preserving, so each CTA resamples its own band
 // and the only data that crosses CTAs is ONE halo row, the margin and the arg-max,
 // written straight into the peer's shared memory (DSMEM) before a cluster barrier.
 //
-// Per image (see jet.cu for the algorithm and reference citations):
-//   setup   : 1-D bulk async copy of the parameter block (double buffered), warp 0
-//             builds conic coefficients + bounding boxes.
-//   phase 1 : warps pull 4-row x 128-column tiles from a shared counter; 16 pixels per
-//             lane, ~6.5 issue slots per MUFU.EX2, components culled per tile.
-//   zoom    : margin -> tap table -> H pass in place (column taps live in registers) ->
-//             halo row exchange -> V pass (max) -> V pass (scale + single write).
+// Per image (see jet.cu for the algorithm and the reference citations):
+//   setup   : 1-D bulk async copy of the parameter block (double buffered).  Warp 0
+//             builds, one image AHEAD and off the critical path, the float32 conic
+//             coefficients and, per component and 8-row group, the exact column
+//             interval of its > tau footprint (the culling table).
+//   phase 1 : warps pull 8-row x 64-column tiles from a shared counter; 16 pixels per
+//             lane, ~6.4 issue slots per MUFU.EX2; a component is skipped when its
+//             column interval for the tile's row group misses the tile.
+//   zoom    : margin (DSMEM atomicMin) -> tap table -> H pass in place, rows pulled
+//             dynamically, column taps in registers -> halo row exchange -> ONE V pass
+//             whose results stay in registers -> arg-max (DSMEM atomicMax) -> scaled
+//             128-bit stores.  The float64 peak for the labels is evaluated by one
+//             warp while the others already render the next image.
 #include <cooperative_groups.h>
 
 #include "jet_common.cuh"
@@ -26,22 +32,27 @@ namespace v2 {
 
 constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
-constexpr int kTileRows = 4;
+constexpr int kTileRows = 8;
+constexpr int kTileCols = 64;   // 2 columns per lane
+constexpr int kMaxBand = 128;   // rows per CTA band (V-pass results live in registers)
+constexpr int kRowsPerWarp = kMaxBand / kWarps;
+constexpr int kMaxGroups = kMaxBand / kTileRows;
 
 struct __align__(16) Fixed2 {
-  double params[2][kMaxSlots * RSB_JET_PARAM_STRIDE];
-  Coef coef[kMaxSlots];
-  double pix64[16 * kMaxSlots];  // float64 slot terms of the <= 16 raw pixels under the peak
-  uint64_t bar[2];
-  unsigned long long xbest[2][2];  // [image parity][cluster rank] arg-max keys
-  unsigned long long red_u[kWarps];
-  double peak;
-  int xmargin[2][2];             // [image parity][cluster rank] margins
-  int red_i[kWarps];
-  int nlive;
+  double params[3][kMaxSlots * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
+  Coef coef[2][kMaxSlots];                             // double buffered, built one image ahead
+  int span[2][kMaxSlots][kMaxGroups];  // lo | hi << 16 column interval per (live slot, row group)
+  double pix64[20 * kMaxSlots];     // peak64 scratch: 16 pixel x slot terms + 4 per-slot rotations
+  uint64_t bar[3];
+  unsigned long long xbest[2][2];   // [image parity][rank] arg-max key of each band
+  unsigned long long lbest;         // this CTA's running arg-max key
+  int xmargin[2][2];                // [image parity][rank] margin of each band
+  int lmargin;                      // this CTA's running margin
+  int nlive[2];
   int next_tile;
-  int foot_lo, foot_hi;          // output coordinates with a non-zero tap
-  float delta;
+  int next_row;
+  int foot_lo, foot_hi;             // output coordinates with a non-zero tap
+  float delta[2];
 };
 
 // one slot's float64 value at a raw pixel, operation order of gauss.py:77-88
@@ -62,7 +73,7 @@ __device__ __forceinline__ unsigned long long best_key(float v, int idx) {
   return ((unsigned long long)__float_as_uint(fmaxf(v, 0.f)) << 32) | (unsigned)(~(unsigned)idx);
 }
 
-__device__ __forceinline__ void store_out4(void* out_row, bool f64, int c0, int N, bool vec,
+__device__ __forceinline__ void store_out4(char* out_row, bool f64, int c0, int N, bool vec,
                                            float4 v) {
   if (!f64) {
     float* row = reinterpret_cast<float*>(out_row);
@@ -89,14 +100,166 @@ __device__ __forceinline__ void store_out4(void* out_row, bool f64, int c0, int 
   }
 }
 
-// local storage row of a V-pass tap; only zero-weight taps can fall outside [0, H]
-__device__ __forceinline__ int lrow(int l, int H) { return min(max(l, 0), H); }
+// ---- warp 0: parameter block -> compacted coefficients + culling spans ------------
+// Ellipse of the > tau footprint: z^T M z <= T^2 with z = (dr, dc).  For a row range
+// the covered columns are [min cl, max cr], cl/cr = centre line -/+ half width; cr is
+// concave in dr, so its maximum over the range is the ellipse's rightmost point if that
+// row lies in the range, else the larger end value (mirror image for cl).
+__device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
+                                    int H, int lane) {
+  float amax = 0.f;
+  for (int k = lane; k < slots; k += 32) amax = fmaxf(amax, fabsf((float)P[k * 6]));
+  amax = warp_max(amax);
+  const double tau = 2e-8 * (double)amax;  // <= 19 x 2e-8 of the peak is dropped in total
+  const int ngroups = (H + kTileRows - 1) / kTileRows;
+  int base = 0;
+  for (int k0 = 0; k0 < slots; k0 += 32) {
+    const int k = k0 + lane;
+    bool live = false;
+    Coef c;
+    double Mrr = 0, Mcc = 0, Mrc = 0, T2 = 0, ec = 0, x = 0, y = 0;
+    bool degenerate = false;
+    if (k < slots) {
+      const double* p = P + k * 6;
+      const double amp = p[0], sx = p[3], sy = p[4];
+      x = p[1];
+      y = p[2];
+      if (amp != 0.0 && fabs(amp) > tau) {
+        double sr, cr;
+        sincos(p[5], &sr, &cr);
+        const double iu = 1.0 / (sy * sy), iv = 1.0 / (sx * sx);
+        Mrr = cr * cr * iu + sr * sr * iv;
+        Mcc = sr * sr * iu + cr * cr * iv;
+        Mrc = sr * cr * (iv - iu);
+        const double h = 0.5 * 1.4426950408889634;  // exponent = -(z^T M z)/2 * log2(e)
+        c.A = (float)(-h * Mcc);
+        c.C = (float)(-h * Mrr);
+        c.B = (float)(-2.0 * h * Mrc);
+        c.amp = (float)amp;
+        const double yr = rint(y), xr = rint(x);
+        c.irf = (float)yr;
+        c.fr = (float)(y - yr);
+        c.icf = (float)xr;
+        c.fc = (float)(x - xr);
+        T2 = 2.0 * log(fabs(amp) / tau);
+        const double det = Mrr * Mcc - Mrc * Mrc;
+        const double er = sqrt(T2 * Mcc / det);
+        ec = sqrt(T2 * Mrr / det);
+        degenerate = !(isfinite(er) && isfinite(ec));
+        const double lo_r = fmax(floor(y - er) - 1.0, 0.0), hi_r = fmin(ceil(y + er) + 1.0, N - 1.0);
+        const double lo_c = fmax(floor(x - ec) - 1.0, 0.0), hi_c = fmin(ceil(x + ec) + 1.0, N - 1.0);
+        if (degenerate) {
+          live = true;
+          c.r0 = 0; c.r1 = N - 1; c.c0 = 0; c.c1 = N - 1;
+        } else if (lo_r <= hi_r && lo_c <= hi_c) {
+          live = true;
+          c.r0 = (int)lo_r; c.r1 = (int)hi_r; c.c0 = (int)lo_c; c.c1 = (int)hi_c;
+        }
+      }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, live);
+    if (live) {
+      const int pos = base + __popc(mask & ((1u << lane) - 1u));
+      sm.coef[cb][pos] = c;
+      // float32 is plenty here: the interval is widened by one pixel on each side
+      const float fMrr = (float)Mrr, fMcc = (float)Mcc, fMrc = (float)Mrc, fT2 = (float)T2;
+      const float fdet = fMrr * fMcc - fMrc * fMrc, fec = (float)ec, fx = (float)x, fy = (float)y;
+      const float dr_right = -fMrc * fec / fMrr;  // row offset of the rightmost point
+      const float inv_cc = 1.f / fMcc, slope = -fMrc * inv_cc;
+      for (int g = 0; g < ngroups; ++g) {
+        const int ga = max(R0 + g * kTileRows, c.r0);
+        const int gb = min(min(R0 + g * kTileRows + kTileRows - 1, R0 + H - 1), c.r1);
+        int packed = 0x7fff;  // lo = 32767 > hi = 0: empty
+        if (ga <= gb) {
+          int lo_i = c.c0, hi_i = c.c1;
+          if (!degenerate) {
+            const float da = (float)ga - fy, db = (float)gb - fy;
+            const float hwa = sqrtf(fmaxf(fT2 * fMcc - fdet * da * da, 0.f)) * inv_cc;
+            const float hwb = sqrtf(fmaxf(fT2 * fMcc - fdet * db * db, 0.f)) * inv_cc;
+            const float cla = slope * da, clb = slope * db;
+            const float hi = (da <= dr_right && dr_right <= db) ? fec : fmaxf(cla + hwa, clb + hwb);
+            const float lo = (da <= -dr_right && -dr_right <= db) ? -fec : fminf(cla - hwa, clb - hwb);
+            lo_i = max((int)floorf(fx + lo) - 1, c.c0);
+            hi_i = min((int)ceilf(fx + hi) + 1, c.c1);
+          }
+          if (lo_i <= hi_i) packed = lo_i | (hi_i << 16);
+        }
+        sm.span[cb][pos][g] = packed;
+      }
+    }
+    base += __popc(mask);
+  }
+  if (lane == 0) {
+    sm.nlive[cb] = base;
+    sm.delta[cb] = 2e-6f * fmaxf(1.f, amax);
+  }
+}
 
-// column taps of 4 consecutive output columns, kept in registers during the H pass
-struct ColTaps {
-  float w[4][4];  // [tap][column]
-  int ia[4];      // a | a1 << 16   (taps 0, 1)
-  int ib[4];      // b | b1 << 16   (taps 2, 3)
+// ---- float64 peak (jet_max) for the labels, one warp -------------------------------
+// The float32 image fixes WHERE the maximum is; its float64 value is recomputed from the
+// parameters: <= 4x4 raw pixels x slots (operation order of gauss.py:77-88), combined with
+// float64 tap weights.  scratch: >= 16*slots + 4*slots doubles.
+__device__ inline double peak64(double* scratch, const double* P, int slots, int N, bool zoom,
+                                int zpad, int margin, unsigned long long image_best, int lane) {
+  const unsigned idx = ~(unsigned)(image_best & 0xffffffffull);
+  const int pr = (int)(idx / (unsigned)N), pc = (int)(idx % (unsigned)N);
+  double* rot = scratch + 16 * slots;  // per slot: cr, sr, ra, rb
+  for (int k = lane; k < slots; k += 32) {
+    const double* p = P + 6 * k;
+    const double cr = cos(p[5]), sr = sin(p[5]);
+    rot[4 * k] = cr;
+    rot[4 * k + 1] = sr;
+    rot[4 * k + 2] = p[2] * cr - p[1] * sr;
+    rot[4 * k + 3] = p[2] * sr + p[1] * cr;
+  }
+  __syncwarp();
+  Taps64 tr, tc;
+  int npx = 1;
+  if (zoom) {
+    tr = composite_taps(pr, N, margin, zpad);
+    tc = composite_taps(pc, N, margin, zpad);
+    npx = 16;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      tr.i[k] = pr; tc.i[k] = pc;
+      tr.w[k] = tc.w[k] = (k == 0) ? 1.0 : 0.0;
+    }
+  }
+  for (int e = lane; e < npx * slots; e += 32) {
+    const int px = e / slots, k = e - px * slots;
+    const int i = px >> 2, j = px & 3;
+    const double* p = P + 6 * k;
+    double v = 0.0;
+    if (p[0] != 0.0 && tr.w[i] * tc.w[j] != 0.0) {
+      const int r = tr.i[i], c = tc.i[j];
+      const double cr = rot[4 * k], sr = rot[4 * k + 1];
+      const double ua = r * cr - c * sr, ub = r * sr + c * cr;
+      const double a = (rot[4 * k + 2] - ua) / p[4], b = (rot[4 * k + 3] - ub) / p[3];
+      v = p[0] * exp(-(a * a + b * b) / 2.0);
+    }
+    scratch[e] = v;
+  }
+  __syncwarp();
+  double s = 0.0;
+  if (lane < npx)
+    for (int k = 0; k < slots; ++k) s += scratch[lane * slots + k];  // slot order
+  double acc = 0.0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    double h = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) h += tc.w[j] * __shfl_sync(0xffffffffu, s, (i * 4 + j) & (npx - 1));
+    acc += tr.w[i] * h;
+  }
+  __syncwarp();
+  return acc;
+}
+
+// unpacked taps of one output coordinate
+struct Tap4 {
+  float w[4];
+  int i[4];
 };
 
 template <int kCluster, int NS>
@@ -106,15 +269,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const int N = a.size, pitch = a.pitch, slots = a.slots;
   const int npad = (N + 3) & ~3;
   float* tab_w = reinterpret_cast<float*>(smem_raw + sizeof(Fixed2));  // [4][npad]
-  int* tab_a = reinterpret_cast<int*>(tab_w + 4 * npad);               // [npad] taps 0,1
-  int* tab_b = tab_a + npad;                                           // [npad] taps 2,3
-  float* raw = reinterpret_cast<float*>(tab_b + npad);  // [H (+1 halo)][pitch]
+  int* tab_i = reinterpret_cast<int*>(tab_w + 4 * npad);               // [4][npad] absolute index
+  float* raw = reinterpret_cast<float*>(tab_i + 4 * npad);             // [H (+1 halo)][pitch]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0;
   const int cid = blockIdx.x / kCluster, nclusters = gridDim.x / kCluster;
-  const int H = N / kCluster;             // rows of this CTA's band (N even when kCluster == 2)
-  const int R0 = rank * H;                // first absolute row of the band
+  const int H = N / kCluster;                // rows of this CTA's band (N even when kCluster == 2)
+  const int R0 = rank * H;                   // first absolute row of the band
   const int base = (rank == 0) ? 0 : H - 1;  // absolute row stored at raw row 0 (rank 1: halo)
   Fixed2* peer = nullptr;
   float* peer_raw = nullptr;
@@ -123,9 +285,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     peer = cluster.map_shared_rank(&sm, rank ^ 1);
     peer_raw = cluster.map_shared_rank(raw, rank ^ 1);
   }
+  auto image_sync = [&]() {  // all threads of the image's CTAs
+    if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
+  };
 
   const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
-  const int strips = (N + kStrip - 1) / kStrip;
+  const int strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
+  const int tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
+  const int ntiles = ((H + kTileRows - 1) / kTileRows) * tcols;
   const bool vec = (N & 3) == 0;
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
@@ -134,75 +301,102 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   if (tid == 0) {
     mbar_init(&sm.bar[0], 1);
     mbar_init(&sm.bar[1], 1);
+    mbar_init(&sm.bar[2], 1);
     fence_mbar_init();
+    sm.lmargin = N;
+    sm.lbest = 0ull;
+    sm.next_tile = 0;
+    sm.next_row = 0;
   }
   __syncthreads();
+  auto prefetch = [&](int image, int pb) {  // one thread: parameter block -> params[pb]
+    fence_proxy_async();
+    mbar_expect_tx(&sm.bar[pb], pbytes);
+    bulk_g2s(sm.params[pb], a.params + (size_t)image * slots * 6, pbytes, &sm.bar[pb]);
+  };
   if (tid == 0 && cid < a.n) {
-    mbar_expect_tx(&sm.bar[0], pbytes);
-    bulk_g2s(sm.params[0], a.params + (size_t)cid * slots * 6, pbytes, &sm.bar[0]);
+    prefetch(cid, 0);
+    if (cid + nclusters < a.n) prefetch(cid + nclusters, 1);
   }
-  if constexpr (kCluster > 1) cg::this_cluster().sync();  // peer CTA is resident
+  if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
+    mbar_wait(&sm.bar[0], 0);
+    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane);
+  }
+  image_sync();  // peer CTA is resident
+
+  // label job of the previous image (warp 1 of rank 0 runs it during the next phase 1)
+  bool prev_valid = false, prev_zoom = false;
+  int prev_img = 0, prev_pb = 0, prev_margin = 0, prev_zpad = 0;
+  unsigned long long prev_best = 0ull;
+  auto label_job = [&]() {
+    double peak = 1.0;
+    if (normalize)
+      peak = peak64(sm.pix64, sm.params[prev_pb], slots, N, prev_zoom, prev_zpad, prev_margin,
+                    prev_best, lane);
+    if (lane == 0) {
+      a.margin[prev_img] = prev_margin;
+      a.peak[prev_img] = peak;
+    }
+  };
 
   int it = 0;
   for (int img = cid; img < a.n; img += nclusters, ++it) {
-    const int buf = it & 1;
-    if (tid == 0) {
-      sm.next_tile = 0;
-      if (img + nclusters < a.n) {
-        fence_proxy_async();
-        mbar_expect_tx(&sm.bar[buf ^ 1], pbytes);
-        bulk_g2s(sm.params[buf ^ 1], a.params + (size_t)(img + nclusters) * slots * 6, pbytes,
-                 &sm.bar[buf ^ 1]);
-      }
+    const int buf = it & 1;   // coefficient / exchange-slot parity
+    const int pb = it % 3;    // parameter buffer
+    mbar_wait(&sm.bar[pb], (it / 3) & 1);
+    __syncthreads();  // (A) coef/span/nlive of this image visible; raw free for reuse
+    if (warp == 0 && img + nclusters < a.n) {
+      // next image's coefficients and culling spans, hidden behind this image's phase 1
+      const int nb = (it + 1) % 3;
+      mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
+      build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane);
     }
-    mbar_wait(&sm.bar[buf], (it >> 1) & 1);
-    const double* P = sm.params[buf];
+    if (warp == 1) {
+      // previous image's labels, then its parameter buffer is free for image it+2
+      if (rank == 0 && prev_valid) label_job();
+      if (lane == 0 && img + 2 * nclusters < a.n) prefetch(img + 2 * nclusters, (it + 2) % 3);
+    }
+    const double* P = sm.params[pb];
     const int zpad = a.zoom_pad[img];
     const bool zoom = zpad >= 0;
-    if (warp == 0) build_coefs(sm, P, slots, N, lane);
-    __syncthreads();
-    const int nlive = sm.nlive;
-    const float thr = (float)kEdgeThr, delta = sm.delta;
+    const int nlive = sm.nlive[buf];
+    const float thr = (float)kEdgeThr, delta = sm.delta[buf];
+    const Coef* coef = sm.coef[buf];
+    const int (*span)[kMaxGroups] = sm.span[buf];
 
-    // ---------------- phase 1: splat this CTA's band, 4 x 128 tiles ------------------
+    // ---------------- phase 1: splat this CTA's band, 8 x 64 tiles ------------------
     int my_margin = N;
     unsigned long long my_best = 0ull;
     float best_v = -1.f;
-    const int ntiles = ((H + kTileRows - 1) / kTileRows) * strips;
     for (;;) {
       int t = 0;
       if (lane == 0) t = atomicAdd(&sm.next_tile, 1);
       t = __shfl_sync(0xffffffffu, t, 0);
       if (t >= ntiles) break;
-      const int tr = t / strips, s = t - tr * strips;
-      const int r0 = R0 + tr * kTileRows, sc0 = s * kStrip, c0 = sc0 + 4 * lane;
+      const int g = t / tcols, tc = t - g * tcols;
+      const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
       const float r0f = (float)r0, c0f = (float)c0;
-      float acc[kTileRows][4];
+      float acc[kTileRows][2];
 #pragma unroll
-      for (int i = 0; i < kTileRows; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+      for (int i = 0; i < kTileRows; ++i) acc[i][0] = acc[i][1] = 0.f;
       for (int k = 0; k < nlive; ++k) {
-        const int4 bb = *reinterpret_cast<const int4*>(&sm.coef[k].r0);
-        if (r0 > bb.y || r0 + kTileRows - 1 < bb.x || sc0 > bb.w || sc0 + kStrip - 1 < bb.z)
-          continue;  // warp-uniform cull
-        const float4 q = *reinterpret_cast<const float4*>(&sm.coef[k].A);    // A B C amp
-        const float4 ct = *reinterpret_cast<const float4*>(&sm.coef[k].irf);  // irf fr icf fc
-        const float dc = (c0f - ct.z) - ct.w;
-        float Pj[4], Qj[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float d = dc + (float)j;
-          Qj[j] = q.y * d;
-          Pj[j] = q.x * d * d;
-        }
+        const int sp = span[k][g];
+#ifndef RSB_DBG_NOSPAN
+        if ((sp >> 16) < tc0 || (sp & 0xffff) > tc0 + kTileCols - 1) continue;  // warp-uniform
+#else
+        (void)sp;
+#endif
+        const float4 q = *reinterpret_cast<const float4*>(&coef[k].A);     // A B C amp
+        const float4 ct = *reinterpret_cast<const float4*>(&coef[k].irf);  // irf fr icf fc
+        const float d0 = (c0f - ct.z) - ct.w, d1 = d0 + 1.f;
+        const float Q0 = q.y * d0, Q1 = q.y * d1;
+        const float P0 = q.x * d0 * d0, P1 = q.x * d1 * d1;
 #pragma unroll
         for (int i = 0; i < kTileRows; ++i) {
           const float dr = ((r0f + (float)i) - ct.x) - ct.y;
           const float Cq = q.z * dr * dr;
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            acc[i][j] = fmaf(q.w, ex2(fmaf(dr, Qj[j], Pj[j] + Cq)), acc[i][j]);
+          acc[i][0] = fmaf(q.w, ex2(fmaf(dr, Q0, P0 + Cq)), acc[i][0]);
+          acc[i][1] = fmaf(q.w, ex2(fmaf(dr, Q1, P1 + Cq)), acc[i][1]);
         }
       }
       if (c0 < N) {
@@ -210,14 +404,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         for (int i = 0; i < kTileRows; ++i) {
           const int r = r0 + i;
           if (r >= R0 + H) break;
-          *reinterpret_cast<float4*>(raw + (size_t)(r - base) * pitch + c0) =
-              make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-          const float top = fmaxf(fmaxf(acc[i][0], acc[i][1]), fmaxf(acc[i][2], acc[i][3]));
+          *reinterpret_cast<float2*>(raw + (size_t)(r - base) * pitch + c0) =
+              make_float2(acc[i][0], acc[i][1]);
+          const float top = fmaxf(acc[i][0], acc[i][1]);
           if (zoom) {
             if (top > thr - delta) {
               const int db = min(r, N - 1 - r);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int j = 0; j < 2; ++j) {
                 const int c = c0 + j;
                 const int d = min(db, min(c, N - 1 - c));
                 if (c < N && d < my_margin && acc[i][j] > thr - delta) {
@@ -229,7 +423,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
             }
           } else if (normalize && top >= best_v) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < 2; ++j) {
               if (c0 + j < N) {
                 const unsigned long long key = best_key(acc[i][j], r * N + c0 + j);
                 my_best = key > my_best ? key : my_best;
@@ -241,42 +435,30 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       }
     }
 
-    double peak = 1.0;
     int margin = 0;
     char* out = reinterpret_cast<char*>(a.out) + (size_t)img * N * N * esz;
+    unsigned long long image_best = 0ull;  // arg-max key of the final image (normalize only)
 
     if (!zoom) {
       // ------------- plain branch ---------------------------------------------------
       if (normalize) {
         my_best = warp_max_u64(my_best);
-        if (lane == 0) sm.red_u[warp] = my_best;
-        __syncthreads();
-        if (warp == 0) {
-          unsigned long long b = lane < kWarps ? sm.red_u[lane] : 0ull;
-          b = warp_max_u64(b);
-          if (lane == 0) {
-            sm.xbest[buf][rank] = b;
-            if constexpr (kCluster > 1) peer->xbest[buf][rank] = b;
-          }
-        }
-        if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
-        unsigned long long b = sm.xbest[buf][0];
-        if constexpr (kCluster > 1) b = sm.xbest[buf][1] > b ? sm.xbest[buf][1] : b;
-        const unsigned idx = ~(unsigned)(b & 0xffffffffull);
-        const int pr = (int)(idx / (unsigned)N), pc = (int)(idx % (unsigned)N);
-        for (int k = tid; k < slots; k += kThreads) sm.pix64[k] = gauss64(P + 6 * k, pr, pc);
+        if (lane == 0) atomicMax(&sm.lbest, my_best);
         __syncthreads();
         if (tid == 0) {
-          double s = 0.0;
-          for (int k = 0; k < slots; ++k) s += sm.pix64[k];
-          sm.peak = s;
+          const unsigned long long b = sm.lbest;
+          sm.xbest[buf][rank] = b;
+          if constexpr (kCluster > 1) peer->xbest[buf][rank] = b;
         }
-        __syncthreads();
-        peak = sm.peak;
-      } else {
-        __syncthreads();
       }
-      const float inv = normalize ? (float)(1.0 / peak) : 1.f;
+      image_sync();  // (C') phase 1 done everywhere, arg-max complete
+      image_best = sm.xbest[buf][0];
+      if constexpr (kCluster > 1) image_best = sm.xbest[buf][1] > image_best ? sm.xbest[buf][1] : image_best;
+      if (tid == 0) {
+        sm.next_tile = 0;
+        sm.lbest = 0ull;
+      }
+      const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
       for (int e = tid; e < H * q4; e += kThreads) {
         const int rl = e / q4, c0 = (e - rl * q4) << 2;
@@ -288,44 +470,49 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     } else {
       // ------------- zoom branch ------------------------------------------------------
       my_margin = warp_min(my_margin);
-      if (lane == 0) sm.red_i[warp] = my_margin;
+      if (lane == 0 && my_margin < N) atomicMin(&sm.lmargin, my_margin);
       __syncthreads();
-      if (warp == 0) {
-        int m = lane < kWarps ? sm.red_i[lane] : N;
-        m = warp_min(m);
-        if (lane == 0) {
-          sm.xmargin[buf][rank] = m;
-          if constexpr (kCluster > 1) peer->xmargin[buf][rank] = m;
-          sm.foot_lo = N;
-          sm.foot_hi = -1;
-        }
+      if (tid == 0) {
+        const int m = sm.lmargin;
+        sm.xmargin[buf][rank] = m;
+        if constexpr (kCluster > 1) peer->xmargin[buf][rank] = m;
       }
-      if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
+      image_sync();  // (C) phase 1 done everywhere, margin complete
       margin = sm.xmargin[buf][0];
       if constexpr (kCluster > 1) margin = min(margin, sm.xmargin[buf][1]);
       if (margin >= N) margin = 0;  // empty mask -> idx 0 (argmax of an all-false array)
+      if (tid == 0) {
+        sm.lmargin = N;
+        sm.next_tile = 0;
+        sm.next_row = 0;
+        sm.foot_lo = N;
+        sm.foot_hi = -1;
+      }
+      __syncthreads();  // foot_* initialised before the atomics below
 
       // composite tap table (float64 math, float32 weights) + output footprint
       {
         int lo = N, hi = -1;
         for (int d = tid; d < npad; d += kThreads) {
           float w[4] = {0.f, 0.f, 0.f, 0.f};
-          int ia = margin | (margin << 16), ib = ia;
+          int ix[4] = {margin, margin, margin, margin};
           if (d < N) {
             const Taps64 t = composite_taps(d, N, margin, zpad);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) w[k] = (float)t.w[k];
-            ia = t.i[0] | (t.i[1] << 16);
-            ib = t.i[2] | (t.i[3] << 16);
+            for (int k = 0; k < 4; ++k) {
+              w[k] = (float)t.w[k];
+              ix[k] = t.i[k];
+            }
             if (w[0] != 0.f || w[1] != 0.f || w[2] != 0.f || w[3] != 0.f) {
               lo = min(lo, d);
               hi = max(hi, d);
             }
           }
 #pragma unroll
-          for (int k = 0; k < 4; ++k) tab_w[k * npad + d] = w[k];
-          tab_a[d] = ia;
-          tab_b[d] = ib;
+          for (int k = 0; k < 4; ++k) {
+            tab_w[k * npad + d] = w[k];
+            tab_i[k * npad + d] = ix[k];
+          }
         }
         lo = warp_min(lo);
         hi = -warp_min(-hi);
@@ -334,38 +521,35 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           if (hi >= 0) atomicMax(&sm.foot_hi, hi);
         }
       }
-      __syncthreads();
+      __syncthreads();  // (D)
       const int flo = sm.foot_lo, fhi = sm.foot_hi;  // empty footprint: flo = N, fhi = -1
 
-      // H pass, in place: row r of raw becomes row r of T.  Column taps stay in registers.
+
+      // H pass, in place: row r of raw becomes row r of T.  Column taps stay in registers,
+      // rows are pulled from a shared counter (warp 0 joins late).
       {
-        ColTaps ct[NS];
+        Tap4 ct[NS][4];
         bool act[NS];
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
           const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
           act[s] = (s < strips) && sc0 <= fhi && sc0 + kStrip - 1 >= flo;
-          if (act[s] && c0 < N) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = min(c0 + j, npad - 1);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const float4 w = *reinterpret_cast<const float4*>(tab_w + k * npad + c0);
-              ct[s].w[k][0] = w.x; ct[s].w[k][1] = w.y; ct[s].w[k][2] = w.z; ct[s].w[k][3] = w.w;
-            }
-            const int4 ia = *reinterpret_cast<const int4*>(tab_a + c0);
-            const int4 ib = *reinterpret_cast<const int4*>(tab_b + c0);
-            ct[s].ia[0] = ia.x; ct[s].ia[1] = ia.y; ct[s].ia[2] = ia.z; ct[s].ia[3] = ia.w;
-            ct[s].ib[0] = ib.x; ct[s].ib[1] = ib.y; ct[s].ib[2] = ib.z; ct[s].ib[3] = ib.w;
-          } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-#pragma unroll
-              for (int k = 0; k < 4; ++k) ct[s].w[k][j] = 0.f;
-              ct[s].ia[j] = ct[s].ib[j] = margin | (margin << 16);
+              ct[s][j].w[k] = (act[s] && c0 + j < N) ? tab_w[k * npad + c] : 0.f;
+              ct[s][j].i[k] = act[s] ? tab_i[k * npad + c] : margin;
             }
           }
         }
         const int rlo = max(R0, margin), rhi = min(R0 + H, N - margin);
-        for (int r = rlo + warp; r < rhi; r += kWarps) {
+        for (;;) {
+          int r = 0;
+          if (lane == 0) r = atomicAdd(&sm.next_row, 1);
+          r = __shfl_sync(0xffffffffu, r, 0) + rlo;
+          if (r >= rhi) break;
           float* row = raw + (size_t)(r - base) * pitch;
           float4 res[NS];
 #pragma unroll
@@ -374,11 +558,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
             if (act[s]) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                const int ia = ct[s].ia[j], ib = ct[s].ib[j];
-                o[j] = ct[s].w[0][j] * row[ia & 0xffff];
-                o[j] = fmaf(ct[s].w[1][j], row[ia >> 16], o[j]);
-                o[j] = fmaf(ct[s].w[2][j], row[ib & 0xffff], o[j]);
-                o[j] = fmaf(ct[s].w[3][j], row[ib >> 16], o[j]);
+                o[j] = ct[s][j].w[0] * row[ct[s][j].i[0]];
+                o[j] = fmaf(ct[s][j].w[1], row[ct[s][j].i[1]], o[j]);
+                o[j] = fmaf(ct[s][j].w[2], row[ct[s][j].i[2]], o[j]);
+                o[j] = fmaf(ct[s][j].w[3], row[ct[s][j].i[3]], o[j]);
               }
             }
             res[s] = make_float4(o[0], o[1], o[2], o[3]);
@@ -391,127 +574,108 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           }
         }
       }
-      __syncthreads();
+      __syncthreads();  // (F) T complete in this band
       if constexpr (kCluster > 1) {
         // halo: my boundary row of T goes into the peer's halo slot
-        const int src = (rank == 0) ? (H - 1) : 1;   // local row index of abs row H-1 / H
-        const int dst = (rank == 0) ? 0 : H;         // peer's halo slot
+        const int src = (rank == 0) ? (H - 1) : 1;  // local index of absolute row H-1 / H
+        const int dst = (rank == 0) ? 0 : H;        // peer's halo slot
         for (int e = tid; e < (pitch >> 2); e += kThreads)
           reinterpret_cast<float4*>(peer_raw + (size_t)dst * pitch)[e] =
               reinterpret_cast<const float4*>(raw + (size_t)src * pitch)[e];
         cg::this_cluster().sync();
       }
 
-      // V pass over the footprint rows of this band
-      const int vr0 = max(R0, flo), vr1 = min(R0 + H - 1, fhi);   // inclusive
-      const int vs0 = flo < N ? flo / kStrip : 0, vs1 = fhi >= 0 ? fhi / kStrip : -1;
-      const int vrows = max(vr1 - vr0 + 1, 0), vstr = max(vs1 - vs0 + 1, 0);
-      float inv = 1.f;
-      if (normalize) {
-        my_best = 0ull;
-        best_v = -1.f;
-        for (int item = warp; item < vrows * vstr; item += kWarps) {
-          const int r = vr0 + item / vstr, s = vs0 + item % vstr;
-          const int c0 = s * kStrip + 4 * lane;
-          if (c0 >= N) continue;
-          const float w0 = tab_w[r], w1 = tab_w[npad + r], w2 = tab_w[2 * npad + r],
-                      w3 = tab_w[3 * npad + r];
-          const int ia = tab_a[r], ib = tab_b[r];
-          const float4 t0 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ia & 0xffff) - base, H) * pitch + c0);
-          const float4 t1 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ia >> 16) - base, H) * pitch + c0);
-          const float4 t2 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ib & 0xffff) - base, H) * pitch + c0);
-          const float4 t3 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ib >> 16) - base, H) * pitch + c0);
-          const float v[4] = {fmaf(w3, t3.x, fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x))),
-                              fmaf(w3, t3.y, fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y))),
-                              fmaf(w3, t3.z, fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z))),
-                              fmaf(w3, t3.w, fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w)))};
-          const float top = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
-          if (top >= best_v) {
+      // V pass: results stay in registers (<= 8 rows x NS strips of 4 columns per lane)
+      const int vr0 = max(R0, flo), vr1 = min(R0 + H - 1, fhi);  // inclusive footprint rows
+      float4 res[kRowsPerWarp][NS];
+      my_best = 0ull;
+      best_v = -1.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (c0 + j < N) {
-                const unsigned long long key = best_key(v[j], r * N + c0 + j);
-                my_best = key > my_best ? key : my_best;
-              }
-            }
-            best_v = __uint_as_float((unsigned)(my_best >> 32));
-          }
-        }
-        my_best = warp_max_u64(my_best);
-        if (lane == 0) sm.red_u[warp] = my_best;
-        __syncthreads();
-        if (warp == 0) {
-          unsigned long long b = lane < kWarps ? sm.red_u[lane] : 0ull;
-          b = warp_max_u64(b);
-          if (lane == 0) {
-            sm.xbest[buf][rank] = b;
-            if constexpr (kCluster > 1) peer->xbest[buf][rank] = b;
-          }
-        }
-        if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
-        unsigned long long b = sm.xbest[buf][0];
-        if constexpr (kCluster > 1) b = sm.xbest[buf][1] > b ? sm.xbest[buf][1] : b;
-        // float64 value of the arg-max pixel: <= 4x4 raw pixels x slots, float64 weights
-        const unsigned idx = ~(unsigned)(b & 0xffffffffull);
-        const int pr = (int)(idx / (unsigned)N), pc = (int)(idx % (unsigned)N);
-        const Taps64 tr = composite_taps(pr, N, margin, zpad);
-        const Taps64 tc = composite_taps(pc, N, margin, zpad);
-        for (int e = tid; e < 16 * slots; e += kThreads) {
-          const int px = e / slots, k = e - px * slots;
-          const int i = px >> 2, j = px & 3;
-          sm.pix64[e] = (tr.w[i] * tc.w[j] != 0.0) ? gauss64(P + 6 * k, tr.i[i], tc.i[j]) : 0.0;
-        }
-        __syncthreads();
-        if (warp == 0) {
-          double s = 0.0;
-          if (lane < 16)
-            for (int k = 0; k < slots; ++k) s += sm.pix64[lane * slots + k];
-          double accd = 0.0;
+      for (int i = 0; i < kRowsPerWarp; ++i) {
+        const int r = R0 + warp + i * kWarps;
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            double h = 0.0;
+        for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < vr0 || r > vr1) continue;  // warp-uniform
+        const float w0 = tab_w[r], w1 = tab_w[npad + r], w2 = tab_w[2 * npad + r],
+                    w3 = tab_w[3 * npad + r];
+        // only zero-weight taps can fall outside this band (+ halo): clamp them
+        const float* p0 = raw + (size_t)min(max(tab_i[r] - base, 0), H) * pitch;
+        const float* p1 = raw + (size_t)min(max(tab_i[npad + r] - base, 0), H) * pitch;
+        const float* p2 = raw + (size_t)min(max(tab_i[2 * npad + r] - base, 0), H) * pitch;
+        const float* p3 = raw + (size_t)min(max(tab_i[3 * npad + r] - base, 0), H) * pitch;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) h += tc.w[j] * __shfl_sync(0xffffffffu, s, i * 4 + j);
-            accd += tr.w[i] * h;
-          }
-          if (lane == 0) sm.peak = accd;
-        }
-        __syncthreads();
-        peak = sm.peak;
-        inv = (float)(1.0 / peak);
-      }
-
-      // V pass B: every output pixel of the band written once, scaled
-      for (int item = warp; item < H * strips; item += kWarps) {
-        const int r = R0 + item / strips, s = item % strips;
-        const int c0 = s * kStrip + 4 * lane;
-        if (c0 >= N) continue;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r >= vr0 && r <= vr1 && s >= vs0 && s <= vs1) {
-          const float w0 = tab_w[r] * inv, w1 = tab_w[npad + r] * inv, w2 = tab_w[2 * npad + r] * inv,
-                      w3 = tab_w[3 * npad + r] * inv;
-          const int ia = tab_a[r], ib = tab_b[r];
-          const float4 t0 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ia & 0xffff) - base, H) * pitch + c0);
-          const float4 t1 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ia >> 16) - base, H) * pitch + c0);
-          const float4 t2 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ib & 0xffff) - base, H) * pitch + c0);
-          const float4 t3 = *reinterpret_cast<const float4*>(raw + (size_t)lrow((ib >> 16) - base, H) * pitch + c0);
+        for (int s = 0; s < NS; ++s) {
+          const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
+          if (!(s < strips && sc0 <= fhi && sc0 + kStrip - 1 >= flo) || c0 >= N) continue;
+          const float4 t0 = *reinterpret_cast<const float4*>(p0 + c0);
+          const float4 t1 = *reinterpret_cast<const float4*>(p1 + c0);
+          const float4 t2 = *reinterpret_cast<const float4*>(p2 + c0);
+          const float4 t3 = *reinterpret_cast<const float4*>(p3 + c0);
+          float4 v;
           v.x = fmaf(w3, t3.x, fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x)));
           v.y = fmaf(w3, t3.y, fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y)));
           v.z = fmaf(w3, t3.z, fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z)));
           v.w = fmaf(w3, t3.w, fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w)));
+          res[i][s] = v;
+          if (normalize) {
+            const float top = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+            if (top >= best_v) {
+              const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (c0 + j < N) {
+                  const unsigned long long key = best_key(vv[j], r * N + c0 + j);
+                  my_best = key > my_best ? key : my_best;
+                }
+              }
+              best_v = __uint_as_float((unsigned)(my_best >> 32));
+            }
+          }
         }
-        store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+      }
+      float inv = 1.f;
+      if (normalize) {
+        my_best = warp_max_u64(my_best);
+        if (lane == 0) atomicMax(&sm.lbest, my_best);
+        __syncthreads();
+        if (tid == 0) {
+          const unsigned long long b = sm.lbest;
+          sm.xbest[buf][rank] = b;
+          if constexpr (kCluster > 1) peer->xbest[buf][rank] = b;
+        }
+        image_sync();  // (G) arg-max complete; nobody reads raw any more
+        image_best = sm.xbest[buf][0];
+        if constexpr (kCluster > 1) image_best = sm.xbest[buf][1] > image_best ? sm.xbest[buf][1] : image_best;
+        if (tid == 0) sm.lbest = 0ull;
+        inv = 1.f / __uint_as_float((unsigned)(image_best >> 32));
+      }
+#pragma unroll
+      for (int i = 0; i < kRowsPerWarp; ++i) {
+        const int r = R0 + warp + i * kWarps;
+        if (r >= R0 + H) continue;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+          const int c0 = s * kStrip + 4 * lane;
+          if (s >= strips || c0 >= N) continue;
+          float4 v = res[i][s];
+          v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+          store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+        }
       }
     }
-    if (tid == 0 && rank == 0) {
-      a.margin[img] = margin;
-      a.peak[img] = peak;
-    }
-    __syncthreads();  // raw / tab / coef / params[buf] are reused by the next image
+
+    // this image's labels are produced during the next image's phase 1
+    prev_valid = true;
+    prev_img = img;
+    prev_pb = pb;
+    prev_margin = margin;
+    prev_zpad = zpad;
+    prev_zoom = zoom;
+    prev_best = image_best;
   }
+  if (rank == 0 && warp == 1 && prev_valid) label_job();
   if constexpr (kCluster > 1) cg::this_cluster().sync();  // no CTA exits while its smem is in use
 }
-
 
 // ------------------------------------------------------------------ host side
 template <int kCluster, int NS>
@@ -519,6 +683,8 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
   auto k = jet2_kernel<kCluster, NS>;
   RSB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   const int sms = sm_count();
+  // CTAs are limited to one per SM by registers (512 threads x 128); small images leave
+  // shared memory for more, but the register file does not
   int nclusters = sms / kCluster;
   if (nclusters > a.n) nclusters = a.n;
   cudaLaunchConfig_t cfg = {};
@@ -543,7 +709,7 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
 static size_t v2_bytes(int size, int cluster) {
   const int npad = (size + 3) & ~3;
   const int rows = size / cluster + (cluster > 1 ? 1 : 0);
-  return sizeof(v2::Fixed2) + (size_t)npad * 24 + (size_t)rows * npad * 4;
+  return sizeof(v2::Fixed2) + (size_t)npad * 32 + (size_t)rows * npad * 4;
 }
 
 bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
@@ -551,13 +717,12 @@ bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
   if (cudaGetDevice(&dev) != cudaSuccess) return false;
   if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess)
     return false;
-  if ((size + kStrip - 1) / kStrip > 3) return false;
-  if (v2_bytes(size, 1) <= (size_t)max_optin) {
+  if (size <= v2::kMaxBand && v2_bytes(size, 1) <= (size_t)max_optin) {
     *cluster = 1;
     *smem_bytes = v2_bytes(size, 1);
     return true;
   }
-  if ((size & 1) == 0 && v2_bytes(size, 2) <= (size_t)max_optin) {
+  if ((size & 1) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
     *cluster = 2;
     *smem_bytes = v2_bytes(size, 2);
     return true;
@@ -566,19 +731,10 @@ bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
 }
 
 int v2_launch(const Args& a, int cluster, size_t smem_bytes, cudaStream_t st) {
-  const int strips = (a.size + kStrip - 1) / kStrip;
-  if (cluster == 1) {
-    switch (strips) {
-      case 1: return v2::launch_v2<1, 1>(a, smem_bytes, st);
-      case 2: return v2::launch_v2<1, 2>(a, smem_bytes, st);
-      default: return v2::launch_v2<1, 3>(a, smem_bytes, st);
-    }
-  }
-  switch (strips) {
-    case 1: return v2::launch_v2<2, 1>(a, smem_bytes, st);
-    case 2: return v2::launch_v2<2, 2>(a, smem_bytes, st);
-    default: return v2::launch_v2<2, 3>(a, smem_bytes, st);
-  }
+  const int strips = (a.size + kStrip - 1) / kStrip;  // <= 2 for size <= 256
+  if (cluster == 1)
+    return strips <= 1 ? v2::launch_v2<1, 1>(a, smem_bytes, st) : v2::launch_v2<1, 2>(a, smem_bytes, st);
+  return strips <= 1 ? v2::launch_v2<2, 1>(a, smem_bytes, st) : v2::launch_v2<2, 2>(a, smem_bytes, st);
 }
 
 }  // namespace jet
