@@ -256,11 +256,39 @@ __device__ inline double peak64(double* scratch, const double* P, int slots, int
   return acc;
 }
 
-// unpacked taps of one output coordinate
-struct Tap4 {
-  float w[4];
-  int i[4];
+// The composite operator has at most THREE consecutive taps: the two zoom-out taps are
+// adjacent zoomed pixels, whose zoom-in taps start at most one raw pixel apart (the zoom-in
+// step is <= 1).  Merged form: base index (<= N-3, so base..base+2 is always in range)
+// and three weights.
+struct Tap3 {
+  float w[3];
+  int i;
 };
+__device__ inline Tap3 merge_taps(const Taps64& t, int N) {
+  Tap3 m;
+  int lo = 0x7fffffff;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (t.w[k] != 0.0) lo = min(lo, t.i[k]);
+  double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+  if (lo == 0x7fffffff) {
+    lo = 0;
+  } else {
+    lo = max(min(lo, N - 3), 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (t.w[k] != 0.0) {
+        const int o = t.i[k] - lo;
+        if (o <= 0) w0 += t.w[k];
+        else if (o == 1) w1 += t.w[k];
+        else w2 += t.w[k];
+      }
+    }
+  }
+  m.i = lo;
+  m.w[0] = (float)w0; m.w[1] = (float)w1; m.w[2] = (float)w2;
+  return m;
+}
 
 template <int kCluster, int NS>
 __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
@@ -268,9 +296,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   Fixed2& sm = *reinterpret_cast<Fixed2*>(smem_raw);
   const int N = a.size, pitch = a.pitch, slots = a.slots;
   const int npad = (N + 3) & ~3;
-  float* tab_w = reinterpret_cast<float*>(smem_raw + sizeof(Fixed2));  // [4][npad]
-  int* tab_i = reinterpret_cast<int*>(tab_w + 4 * npad);               // [4][npad] absolute index
-  float* raw = reinterpret_cast<float*>(tab_i + 4 * npad);             // [H (+1 halo)][pitch]
+  float* tab_w = reinterpret_cast<float*>(smem_raw + sizeof(Fixed2));  // [3][npad] weights
+  int* tab_i = reinterpret_cast<int*>(tab_w + 3 * npad);               // [npad] first tap (absolute)
+  float* raw = reinterpret_cast<float*>(tab_i + npad);                 // [H (+1 halo)][pitch]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0;
@@ -368,47 +396,64 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     int my_margin = N;
     unsigned long long my_best = 0ull;
     float best_v = -1.f;
+    const float inv_tcols = 1.f / (float)tcols;
     for (;;) {
       int t = 0;
       if (lane == 0) t = atomicAdd(&sm.next_tile, 1);
       t = __shfl_sync(0xffffffffu, t, 0);
       if (t >= ntiles) break;
-      const int g = t / tcols, tc = t - g * tcols;
+      const int g = __float2int_rz(((float)t + 0.5f) * inv_tcols), tc = t - g * tcols;
       const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
       const float r0f = (float)r0, c0f = (float)c0;
       float acc[kTileRows][2];
 #pragma unroll
       for (int i = 0; i < kTileRows; ++i) acc[i][0] = acc[i][1] = 0.f;
-      for (int k = 0; k < nlive; ++k) {
-        const int sp = span[k][g];
-#ifndef RSB_DBG_NOSPAN
-        if ((sp >> 16) < tc0 || (sp & 0xffff) > tc0 + kTileCols - 1) continue;  // warp-uniform
-#else
-        (void)sp;
-#endif
-        const float4 q = *reinterpret_cast<const float4*>(&coef[k].A);     // A B C amp
-        const float4 ct = *reinterpret_cast<const float4*>(&coef[k].irf);  // irf fr icf fc
-        const float d0 = (c0f - ct.z) - ct.w, d1 = d0 + 1.f;
-        const float Q0 = q.y * d0, Q1 = q.y * d1;
-        const float P0 = q.x * d0 * d0, P1 = q.x * d1 * d1;
+      // cull: lane k tests live slot k (and k+32) against the tile, the warp walks the hits
+      for (int k0 = 0; k0 < nlive; k0 += 32) {
+        bool hit = false;
+        if (k0 + lane < nlive) {
+          const int sp = span[k0 + lane][g];
+          hit = !((sp >> 16) < tc0 || (sp & 0xffff) > tc0 + kTileCols - 1);
+        }
+        unsigned hits = __ballot_sync(0xffffffffu, hit);
+        while (hits) {
+          const int k = k0 + __ffs(hits) - 1;
+          hits &= hits - 1;
+          const float4 q = *reinterpret_cast<const float4*>(&coef[k].A);     // A B C amp
+          const float4 ct = *reinterpret_cast<const float4*>(&coef[k].irf);  // irf fr icf fc
+          const float d0 = (c0f - ct.z) - ct.w, d1 = d0 + 1.f;
+          const float Q0 = q.y * d0, Q1 = q.y * d1;
+          const float P0 = q.x * d0 * d0, P1 = q.x * d1 * d1;
+          const float dr0 = (r0f - ct.x) - ct.y;
 #pragma unroll
-        for (int i = 0; i < kTileRows; ++i) {
-          const float dr = ((r0f + (float)i) - ct.x) - ct.y;
-          const float Cq = q.z * dr * dr;
-          acc[i][0] = fmaf(q.w, ex2(fmaf(dr, Q0, P0 + Cq)), acc[i][0]);
-          acc[i][1] = fmaf(q.w, ex2(fmaf(dr, Q1, P1 + Cq)), acc[i][1]);
+          for (int i = 0; i < kTileRows; ++i) {
+            const float dr = dr0 + (float)i;
+            const float Cq = q.z * dr * dr;
+            acc[i][0] = fmaf(q.w, ex2(fmaf(dr, Q0, P0 + Cq)), acc[i][0]);
+            acc[i][1] = fmaf(q.w, ex2(fmaf(dr, Q1, P1 + Cq)), acc[i][1]);
+          }
         }
       }
       if (c0 < N) {
+        float tile_top = 0.f;
 #pragma unroll
         for (int i = 0; i < kTileRows; ++i) {
           const int r = r0 + i;
-          if (r >= R0 + H) break;
-          *reinterpret_cast<float2*>(raw + (size_t)(r - base) * pitch + c0) =
-              make_float2(acc[i][0], acc[i][1]);
-          const float top = fmaxf(acc[i][0], acc[i][1]);
-          if (zoom) {
-            if (top > thr - delta) {
+          if (r < R0 + H) {
+            *reinterpret_cast<float2*>(raw + (size_t)(r - base) * pitch + c0) =
+                make_float2(acc[i][0], acc[i][1]);
+            tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
+          }
+        }
+        if (zoom) {
+          // border distance of this lane's nearest-to-border pixel in the tile
+          const int rl = min(r0 + kTileRows - 1, R0 + H - 1);
+          const int dmin = min(min(r0, N - 1 - rl), min(c0, N - 1 - min(c0 + 1, N - 1)));
+          if (tile_top > thr - delta && dmin < my_margin) {
+#pragma unroll
+            for (int i = 0; i < kTileRows; ++i) {
+              const int r = r0 + i;
+              if (r >= R0 + H) break;
               const int db = min(r, N - 1 - r);
 #pragma unroll
               for (int j = 0; j < 2; ++j) {
@@ -421,7 +466,12 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
                 }
               }
             }
-          } else if (normalize && top >= best_v) {
+          }
+        } else if (normalize && tile_top >= best_v) {
+#pragma unroll
+          for (int i = 0; i < kTileRows; ++i) {
+            const int r = r0 + i;
+            if (r >= R0 + H) break;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
               if (c0 + j < N) {
@@ -429,8 +479,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
                 my_best = key > my_best ? key : my_best;
               }
             }
-            best_v = __uint_as_float((unsigned)(my_best >> 32));
           }
+          best_v = __uint_as_float((unsigned)(my_best >> 32));
         }
       }
     }
@@ -494,25 +544,19 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       {
         int lo = N, hi = -1;
         for (int d = tid; d < npad; d += kThreads) {
-          float w[4] = {0.f, 0.f, 0.f, 0.f};
-          int ix[4] = {margin, margin, margin, margin};
+          Tap3 m;
+          m.w[0] = m.w[1] = m.w[2] = 0.f;
+          m.i = 0;
           if (d < N) {
-            const Taps64 t = composite_taps(d, N, margin, zpad);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              w[k] = (float)t.w[k];
-              ix[k] = t.i[k];
-            }
-            if (w[0] != 0.f || w[1] != 0.f || w[2] != 0.f || w[3] != 0.f) {
+            m = merge_taps(composite_taps(d, N, margin, zpad), N);
+            if (m.w[0] != 0.f || m.w[1] != 0.f || m.w[2] != 0.f) {
               lo = min(lo, d);
               hi = max(hi, d);
             }
           }
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            tab_w[k * npad + d] = w[k];
-            tab_i[k * npad + d] = ix[k];
-          }
+          for (int k = 0; k < 3; ++k) tab_w[k * npad + d] = m.w[k];
+          tab_i[d] = m.i;
         }
         lo = warp_min(lo);
         hi = -warp_min(-hi);
@@ -528,7 +572,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       // H pass, in place: row r of raw becomes row r of T.  Column taps stay in registers,
       // rows are pulled from a shared counter (warp 0 joins late).
       {
-        Tap4 ct[NS][4];
+        Tap3 ct[NS][4];
         bool act[NS];
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
@@ -538,10 +582,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           for (int j = 0; j < 4; ++j) {
             const int c = min(c0 + j, npad - 1);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < 3; ++k)
               ct[s][j].w[k] = (act[s] && c0 + j < N) ? tab_w[k * npad + c] : 0.f;
-              ct[s][j].i[k] = act[s] ? tab_i[k * npad + c] : margin;
-            }
+            ct[s][j].i = act[s] ? tab_i[c] : 0;
           }
         }
         const int rlo = max(R0, margin), rhi = min(R0 + H, N - margin);
@@ -558,10 +601,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
             if (act[s]) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                o[j] = ct[s][j].w[0] * row[ct[s][j].i[0]];
-                o[j] = fmaf(ct[s][j].w[1], row[ct[s][j].i[1]], o[j]);
-                o[j] = fmaf(ct[s][j].w[2], row[ct[s][j].i[2]], o[j]);
-                o[j] = fmaf(ct[s][j].w[3], row[ct[s][j].i[3]], o[j]);
+                const float* src = row + ct[s][j].i;
+                o[j] = ct[s][j].w[0] * src[0];
+                o[j] = fmaf(ct[s][j].w[1], src[1], o[j]);
+                o[j] = fmaf(ct[s][j].w[2], src[2], o[j]);
               }
             }
             res[s] = make_float4(o[0], o[1], o[2], o[3]);
@@ -596,13 +639,12 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
         for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < vr0 || r > vr1) continue;  // warp-uniform
-        const float w0 = tab_w[r], w1 = tab_w[npad + r], w2 = tab_w[2 * npad + r],
-                    w3 = tab_w[3 * npad + r];
+        const float w0 = tab_w[r], w1 = tab_w[npad + r], w2 = tab_w[2 * npad + r];
         // only zero-weight taps can fall outside this band (+ halo): clamp them
-        const float* p0 = raw + (size_t)min(max(tab_i[r] - base, 0), H) * pitch;
-        const float* p1 = raw + (size_t)min(max(tab_i[npad + r] - base, 0), H) * pitch;
-        const float* p2 = raw + (size_t)min(max(tab_i[2 * npad + r] - base, 0), H) * pitch;
-        const float* p3 = raw + (size_t)min(max(tab_i[3 * npad + r] - base, 0), H) * pitch;
+        const int l0 = tab_i[r] - base;
+        const float* p0 = raw + (size_t)min(max(l0, 0), H) * pitch;
+        const float* p1 = raw + (size_t)min(max(l0 + 1, 0), H) * pitch;
+        const float* p2 = raw + (size_t)min(max(l0 + 2, 0), H) * pitch;
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
           const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
@@ -610,12 +652,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           const float4 t0 = *reinterpret_cast<const float4*>(p0 + c0);
           const float4 t1 = *reinterpret_cast<const float4*>(p1 + c0);
           const float4 t2 = *reinterpret_cast<const float4*>(p2 + c0);
-          const float4 t3 = *reinterpret_cast<const float4*>(p3 + c0);
           float4 v;
-          v.x = fmaf(w3, t3.x, fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x)));
-          v.y = fmaf(w3, t3.y, fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y)));
-          v.z = fmaf(w3, t3.z, fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z)));
-          v.w = fmaf(w3, t3.w, fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w)));
+          v.x = fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x));
+          v.y = fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y));
+          v.z = fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z));
+          v.w = fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w));
           res[i][s] = v;
           if (normalize) {
             const float top = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
@@ -709,7 +750,7 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
 static size_t v2_bytes(int size, int cluster) {
   const int npad = (size + 3) & ~3;
   const int rows = size / cluster + (cluster > 1 ? 1 : 0);
-  return sizeof(v2::Fixed2) + (size_t)npad * 32 + (size_t)rows * npad * 4;
+  return sizeof(v2::Fixed2) + (size_t)npad * 16 + (size_t)rows * npad * 4;
 }
 
 bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
