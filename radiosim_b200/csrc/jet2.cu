@@ -30,13 +30,20 @@ namespace rsb {
 namespace jet {
 namespace v2 {
 
+#ifdef RSB_TIMELINE
+__device__ long long* g_timeline = nullptr;  // [image][rank][16] clock64 stamps (debug builds)
+#define RSB_STAMP(k) do { if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 16 + (k)] = clock64(); } while (0)
+#else
+#define RSB_STAMP(k) do {} while (0)
+#endif
+
 constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
 constexpr int kTileRows = 8;
 constexpr int kTileCols = 64;   // 2 columns per lane
 constexpr int kMaxBand = 128;   // rows per CTA band (V-pass results live in registers)
 constexpr int kRowsPerWarp = kMaxBand / kWarps;
-constexpr int kMaxGroups = kMaxBand / kTileRows;
+constexpr int kMaxGroups = 2 * kMaxBand / kTileRows;  // row groups of the WHOLE image
 
 struct __align__(16) Fixed2 {
   double params[3][kMaxSlots * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
@@ -44,9 +51,9 @@ struct __align__(16) Fixed2 {
   int span[2][kMaxSlots][kMaxGroups];  // lo | hi << 16 column interval per (live slot, row group)
   double pix64[20 * kMaxSlots];     // peak64 scratch: 16 pixel x slot terms + 4 per-slot rotations
   uint64_t bar[3];
-  unsigned long long xbest[2][2];   // [image parity][rank] arg-max key of each band
+  unsigned long long xval[3][2];    // peer's margin / (unused) / arg-max key, [kind][use parity]
+  uint64_t xbar[3];                 // mbarriers the peer's st.async completes: margin, halo, best
   unsigned long long lbest;         // this CTA's running arg-max key
-  int xmargin[2][2];                // [image parity][rank] margin of each band
   int lmargin;                      // this CTA's running margin
   int nlive[2];
   int next_tile;
@@ -306,21 +313,46 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const int H = N / kCluster;                // rows of this CTA's band (N even when kCluster == 2)
   const int R0 = rank * H;                   // first absolute row of the band
   const int base = (rank == 0) ? 0 : H - 1;  // absolute row stored at raw row 0 (rank 1: halo)
-  Fixed2* peer = nullptr;
-  float* peer_raw = nullptr;
+  // remote (peer CTA) shared-memory addresses for st.async
+  uint32_t peer_xval = 0, peer_xbar = 0, peer_raw = 0;
+  if constexpr (kCluster > 1) {
+    peer_xval = cluster_map(smem_u32(&sm.xval[0][0]), (uint32_t)(rank ^ 1));
+    peer_xbar = cluster_map(smem_u32(&sm.xbar[0]), (uint32_t)(rank ^ 1));
+    peer_raw = cluster_map(smem_u32(raw), (uint32_t)(rank ^ 1));
+  }
+  float* peer_raw_g = raw;     // generic pointers into the peer CTA (remote tile stores)
+  Fixed2* peer_g = &sm;
   if constexpr (kCluster > 1) {
     cg::cluster_group cluster = cg::this_cluster();
-    peer = cluster.map_shared_rank(&sm, rank ^ 1);
-    peer_raw = cluster.map_shared_rank(raw, rank ^ 1);
+    peer_raw_g = cluster.map_shared_rank(raw, rank ^ 1);
+    peer_g = cluster.map_shared_rank(&sm, rank ^ 1);
   }
-  auto image_sync = [&]() {  // all threads of the image's CTAs
-    if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
+  int xuse[3] = {0, 0, 0};  // uses so far of each exchange mbarrier (same in both CTAs)
+  // swap one 64-bit value with the peer CTA (all threads call; value is CTA-uniform)
+  auto exchange = [&](int kind, unsigned long long mine) -> unsigned long long {
+    if constexpr (kCluster == 1) {
+      return mine;
+    } else {
+      const int par = xuse[kind] & 1;
+      if (tid == 0) {
+        st_async_b64(peer_xval + (uint32_t)(kind * 2 + par) * 8u, mine, peer_xbar + (uint32_t)kind * 8u);
+        mbar_expect_tx(&sm.xbar[kind], 8);
+      }
+      mbar_wait(&sm.xbar[kind], (uint32_t)par);
+      xuse[kind]++;
+      return sm.xval[kind][par];
+    }
   };
 
   const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
   const int strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
   const int tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
-  const int ntiles = ((H + kTileRows - 1) / kTileRows) * tcols;
+  // phase-1 tiles cover the WHOLE image and are dealt alternately to the CTAs of the cluster
+  // (a one-sided jet would otherwise leave one band's CTA idle); a tile of the peer's band is
+  // written into the peer's shared memory.
+  const int ngroups_all = (N + kTileRows - 1) / kTileRows;
+  const int ntiles_all = ngroups_all * tcols;
+  const int ntiles = (ntiles_all - rank + kCluster - 1) / kCluster;
   const bool vec = (N & 3) == 0;
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
@@ -330,6 +362,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     mbar_init(&sm.bar[0], 1);
     mbar_init(&sm.bar[1], 1);
     mbar_init(&sm.bar[2], 1);
+    mbar_init(&sm.xbar[0], 1);
+    mbar_init(&sm.xbar[1], 1);
+    mbar_init(&sm.xbar[2], 1);
     fence_mbar_init();
     sm.lmargin = N;
     sm.lbest = 0ull;
@@ -348,9 +383,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   }
   if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
-    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane);
+    build_coefs2(sm, 0, sm.params[0], slots, N, 0, N, lane);
   }
-  image_sync();  // peer CTA is resident
+  // the peer CTA is resident and its mbarriers are initialised before any st.async
+  if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
+  int zpad_next = (cid < a.n) ? a.zoom_pad[cid] : -1;
 
   // label job of the previous image (warp 1 of rank 0 runs it during the next phase 1)
   bool prev_valid = false, prev_zoom = false;
@@ -373,11 +410,16 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const int pb = it % 3;    // parameter buffer
     mbar_wait(&sm.bar[pb], (it / 3) & 1);
     __syncthreads();  // (A) coef/span/nlive of this image visible; raw free for reuse
+    RSB_STAMP(0);
+    if (tid == 0) {  // running reductions of this image (all reads of the previous values are behind A)
+      sm.lbest = 0ull;
+      sm.lmargin = N;
+    }
     if (warp == 0 && img + nclusters < a.n) {
       // next image's coefficients and culling spans, hidden behind this image's phase 1
       const int nb = (it + 1) % 3;
       mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
-      build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane);
+      build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, 0, N, lane);
     }
     if (warp == 1) {
       // previous image's labels, then its parameter buffer is free for image it+2
@@ -385,7 +427,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (lane == 0 && img + 2 * nclusters < a.n) prefetch(img + 2 * nclusters, (it + 2) % 3);
     }
     const double* P = sm.params[pb];
-    const int zpad = a.zoom_pad[img];
+    const int zpad = zpad_next;
+    if (img + nclusters < a.n) zpad_next = a.zoom_pad[img + nclusters];  // latency hidden
     const bool zoom = zpad >= 0;
     const int nlive = sm.nlive[buf];
     const float thr = (float)kEdgeThr, delta = sm.delta[buf];
@@ -402,12 +445,19 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (lane == 0) t = atomicAdd(&sm.next_tile, 1);
       t = __shfl_sync(0xffffffffu, t, 0);
       if (t >= ntiles) break;
-      const int g = __float2int_rz(((float)t + 0.5f) * inv_tcols), tc = t - g * tcols;
-      const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
+      const int ta = t * kCluster + rank;  // tile of the whole image, heaviest (central) rows first
+      const int jg = __float2int_rz(((float)ta + 0.5f) * inv_tcols), tc = ta - jg * tcols;
+      const int gc = (ngroups_all + 1) >> 1;
+      const int g = (jg & 1) ? gc + (jg >> 1) : gc - 1 - (jg >> 1);
+      const int r0 = g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
+      const bool mine = (kCluster == 1) || (r0 >= R0 && r0 < R0 + H);
+      float* dst = mine ? raw + (size_t)(r0 - base) * pitch
+                        : peer_raw_g + (size_t)(r0 - (rank == 0 ? H - 1 : 0)) * pitch;
+      const int rend = min(N, r0 + kTileRows);  // rows of this tile that exist
       const float r0f = (float)r0, c0f = (float)c0;
-      float acc[kTileRows][2];
+      f2 acc2[kTileRows];  // two adjacent pixels per row, packed (FFMA2)
 #pragma unroll
-      for (int i = 0; i < kTileRows; ++i) acc[i][0] = acc[i][1] = 0.f;
+      for (int i = 0; i < kTileRows; ++i) acc2[i] = 0ull;
       // cull: lane k tests live slot k (and k+32) against the tile, the warp walks the hits
       for (int k0 = 0; k0 < nlive; k0 += 32) {
         bool hit = false;
@@ -421,39 +471,49 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           hits &= hits - 1;
           const float4 q = *reinterpret_cast<const float4*>(&coef[k].A);     // A B C amp
           const float4 ct = *reinterpret_cast<const float4*>(&coef[k].irf);  // irf fr icf fc
-          const float d0 = (c0f - ct.z) - ct.w, d1 = d0 + 1.f;
-          const float Q0 = q.y * d0, Q1 = q.y * d1;
-          const float P0 = q.x * d0 * d0, P1 = q.x * d1 * d1;
+          const float d0 = (c0f - ct.z) - ct.w;
+          const f2 d = f2_pack(d0, d0 + 1.f);
+          const f2 Q = f2_mul(f2_pack(q.y, q.y), d);
+          const f2 Pq = f2_mul(f2_mul(f2_pack(q.x, q.x), d), d);
+          const f2 amp2 = f2_pack(q.w, q.w);
           const float dr0 = (r0f - ct.x) - ct.y;
 #pragma unroll
-          for (int i = 0; i < kTileRows; ++i) {
-            const float dr = dr0 + (float)i;
-            const float Cq = q.z * dr * dr;
-            acc[i][0] = fmaf(q.w, ex2(fmaf(dr, Q0, P0 + Cq)), acc[i][0]);
-            acc[i][1] = fmaf(q.w, ex2(fmaf(dr, Q1, P1 + Cq)), acc[i][1]);
+          for (int i = 0; i < kTileRows; i += 2) {
+            // two rows at a time: dr and C dr^2 as a packed pair, then broadcast per row
+            const f2 drp = f2_pack(dr0 + (float)i, dr0 + (float)(i + 1));
+            const f2 Cqp = f2_mul(f2_mul(f2_pack(q.z, q.z), drp), drp);
+            float dra, drb, Cqa, Cqb;
+            f2_unpack(drp, dra, drb);
+            f2_unpack(Cqp, Cqa, Cqb);
+            float ta, tb;
+            f2_unpack(f2_fma(f2_pack(dra, dra), Q, f2_add(Pq, f2_pack(Cqa, Cqa))), ta, tb);
+            acc2[i] = f2_fma(amp2, f2_pack(ex2(ta), ex2(tb)), acc2[i]);
+            f2_unpack(f2_fma(f2_pack(drb, drb), Q, f2_add(Pq, f2_pack(Cqb, Cqb))), ta, tb);
+            acc2[i + 1] = f2_fma(amp2, f2_pack(ex2(ta), ex2(tb)), acc2[i + 1]);
           }
         }
       }
+      float acc[kTileRows][2];
+#pragma unroll
+      for (int i = 0; i < kTileRows; ++i) f2_unpack(acc2[i], acc[i][0], acc[i][1]);
       if (c0 < N) {
         float tile_top = 0.f;
 #pragma unroll
         for (int i = 0; i < kTileRows; ++i) {
-          const int r = r0 + i;
-          if (r < R0 + H) {
-            *reinterpret_cast<float2*>(raw + (size_t)(r - base) * pitch + c0) =
-                make_float2(acc[i][0], acc[i][1]);
+          if (r0 + i < rend) {
+            *reinterpret_cast<float2*>(dst + (size_t)i * pitch + c0) = make_float2(acc[i][0], acc[i][1]);
             tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
           }
         }
         if (zoom) {
           // border distance of this lane's nearest-to-border pixel in the tile
-          const int rl = min(r0 + kTileRows - 1, R0 + H - 1);
+          const int rl = rend - 1;
           const int dmin = min(min(r0, N - 1 - rl), min(c0, N - 1 - min(c0 + 1, N - 1)));
           if (tile_top > thr - delta && dmin < my_margin) {
 #pragma unroll
             for (int i = 0; i < kTileRows; ++i) {
               const int r = r0 + i;
-              if (r >= R0 + H) break;
+              if (r >= rend) break;
               const int db = min(r, N - 1 - r);
 #pragma unroll
               for (int j = 0; j < 2; ++j) {
@@ -471,7 +531,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
           for (int i = 0; i < kTileRows; ++i) {
             const int r = r0 + i;
-            if (r >= R0 + H) break;
+            if (r >= rend) break;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
               if (c0 + j < N) {
@@ -485,6 +545,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       }
     }
 
+    RSB_STAMP(1);  // this warp is out of tiles
     int margin = 0;
     char* out = reinterpret_cast<char*>(a.out) + (size_t)img * N * N * esz;
     unsigned long long image_best = 0ull;  // arg-max key of the final image (normalize only)
@@ -494,20 +555,19 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (normalize) {
         my_best = warp_max_u64(my_best);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
-        __syncthreads();
-        if (tid == 0) {
-          const unsigned long long b = sm.lbest;
-          sm.xbest[buf][rank] = b;
-          if constexpr (kCluster > 1) peer->xbest[buf][rank] = b;
-        }
       }
-      image_sync();  // (C') phase 1 done everywhere, arg-max complete
-      image_best = sm.xbest[buf][0];
-      if constexpr (kCluster > 1) image_best = sm.xbest[buf][1] > image_best ? sm.xbest[buf][1] : image_best;
-      if (tid == 0) {
-        sm.next_tile = 0;
-        sm.lbest = 0ull;
+      __syncthreads();
+      image_best = sm.lbest;
+      if constexpr (kCluster > 1) {
+        // one cluster barrier per image: the peer's tiles have landed in my band, and the
+        // two partial arg-max keys are swapped by plain remote stores ordered by it
+        if (tid == 0) peer_g->xval[1][buf] = image_best;
+        cg::this_cluster().sync();  // (C') phase 1 done everywhere
+        const unsigned long long theirs = sm.xval[1][buf];
+        image_best = theirs > image_best ? theirs : image_best;
       }
+      RSB_STAMP(2);
+      if (tid == 0) sm.next_tile = 0;
       const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
       for (int e = tid; e < H * q4; e += kThreads) {
@@ -522,17 +582,15 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       my_margin = warp_min(my_margin);
       if (lane == 0 && my_margin < N) atomicMin(&sm.lmargin, my_margin);
       __syncthreads();
-      if (tid == 0) {
-        const int m = sm.lmargin;
-        sm.xmargin[buf][rank] = m;
-        if constexpr (kCluster > 1) peer->xmargin[buf][rank] = m;
+      margin = sm.lmargin;
+      if constexpr (kCluster > 1) {
+        if (tid == 0) peer_g->xval[0][buf] = (unsigned long long)(unsigned)margin;
+        cg::this_cluster().sync();  // (C) phase 1 done everywhere, the peer's tiles have landed
+        margin = min(margin, (int)sm.xval[0][buf]);
       }
-      image_sync();  // (C) phase 1 done everywhere, margin complete
-      margin = sm.xmargin[buf][0];
-      if constexpr (kCluster > 1) margin = min(margin, sm.xmargin[buf][1]);
+      RSB_STAMP(2);
       if (margin >= N) margin = 0;  // empty mask -> idx 0 (argmax of an all-false array)
       if (tid == 0) {
-        sm.lmargin = N;
         sm.next_tile = 0;
         sm.next_row = 0;
         sm.foot_lo = N;
@@ -566,6 +624,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         }
       }
       __syncthreads();  // (D)
+      RSB_STAMP(3);
       const int flo = sm.foot_lo, fhi = sm.foot_hi;  // empty footprint: flo = N, fhi = -1
 
 
@@ -617,17 +676,22 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           }
         }
       }
+      RSB_STAMP(4);
       __syncthreads();  // (F) T complete in this band
+      RSB_STAMP(5);
       if constexpr (kCluster > 1) {
         // halo: my boundary row of T goes into the peer's halo slot
         const int src = (rank == 0) ? (H - 1) : 1;  // local index of absolute row H-1 / H
         const int dst = (rank == 0) ? 0 : H;        // peer's halo slot
         for (int e = tid; e < (pitch >> 2); e += kThreads)
-          reinterpret_cast<float4*>(peer_raw + (size_t)dst * pitch)[e] =
-              reinterpret_cast<const float4*>(raw + (size_t)src * pitch)[e];
-        cg::this_cluster().sync();
+          st_async_v4(peer_raw + (uint32_t)(dst * pitch + 4 * e) * 4u,
+                      reinterpret_cast<const float4*>(raw + (size_t)src * pitch)[e], peer_xbar + 8u);
+        if (tid == 0) mbar_expect_tx(&sm.xbar[1], (uint32_t)pitch * 4u);
+        mbar_wait(&sm.xbar[1], (uint32_t)(xuse[1] & 1));
+        xuse[1]++;
       }
 
+      RSB_STAMP(6);
       // V pass: results stay in registers (<= 8 rows x NS strips of 4 columns per lane)
       const int vr0 = max(R0, flo), vr1 = min(R0 + H - 1, fhi);  // inclusive footprint rows
       float4 res[kRowsPerWarp][NS];
@@ -653,10 +717,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           const float4 t1 = *reinterpret_cast<const float4*>(p1 + c0);
           const float4 t2 = *reinterpret_cast<const float4*>(p2 + c0);
           float4 v;
-          v.x = fmaf(w2, t2.x, fmaf(w1, t1.x, w0 * t0.x));
-          v.y = fmaf(w2, t2.y, fmaf(w1, t1.y, w0 * t0.y));
-          v.z = fmaf(w2, t2.z, fmaf(w1, t1.z, w0 * t0.z));
-          v.w = fmaf(w2, t2.w, fmaf(w1, t1.w, w0 * t0.w));
+          {
+            const f2 W0 = f2_pack(w0, w0), W1 = f2_pack(w1, w1), W2 = f2_pack(w2, w2);
+            f2_unpack(f2_fma(W2, f2_pack(t2.x, t2.y), f2_fma(W1, f2_pack(t1.x, t1.y), f2_mul(W0, f2_pack(t0.x, t0.y)))), v.x, v.y);
+            f2_unpack(f2_fma(W2, f2_pack(t2.z, t2.w), f2_fma(W1, f2_pack(t1.z, t1.w), f2_mul(W0, f2_pack(t0.z, t0.w)))), v.z, v.w);
+          }
           res[i][s] = v;
           if (normalize) {
             const float top = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
@@ -674,22 +739,18 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           }
         }
       }
+      RSB_STAMP(7);
       float inv = 1.f;
       if (normalize) {
         my_best = warp_max_u64(my_best);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
-        __syncthreads();
-        if (tid == 0) {
-          const unsigned long long b = sm.lbest;
-          sm.xbest[buf][rank] = b;
-          if constexpr (kCluster > 1) peer->xbest[buf][rank] = b;
-        }
-        image_sync();  // (G) arg-max complete; nobody reads raw any more
-        image_best = sm.xbest[buf][0];
-        if constexpr (kCluster > 1) image_best = sm.xbest[buf][1] > image_best ? sm.xbest[buf][1] : image_best;
-        if (tid == 0) sm.lbest = 0ull;
+        __syncthreads();  // (G) this band's arg-max complete
+        image_best = sm.lbest;
+        const unsigned long long theirs = exchange(2, image_best);
+        image_best = theirs > image_best ? theirs : image_best;
         inv = 1.f / __uint_as_float((unsigned)(image_best >> 32));
       }
+      RSB_STAMP(8);
 #pragma unroll
       for (int i = 0; i < kRowsPerWarp; ++i) {
         const int r = R0 + warp + i * kWarps;
@@ -705,6 +766,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       }
     }
 
+    RSB_STAMP(9);
     // this image's labels are produced during the next image's phase 1
     prev_valid = true;
     prev_img = img;
@@ -763,7 +825,8 @@ bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
     *smem_bytes = v2_bytes(size, 1);
     return true;
   }
-  if ((size & 1) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
+  // two bands of whole 8-row tile groups
+  if ((size % 16) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
     *cluster = 2;
     *smem_bytes = v2_bytes(size, 2);
     return true;
@@ -780,3 +843,10 @@ int v2_launch(const Args& a, int cluster, size_t smem_bytes, cudaStream_t st) {
 
 }  // namespace jet
 }  // namespace rsb
+
+#ifdef RSB_TIMELINE
+extern "C" int rsb_debug_set_timeline(long long* dev_ptr) {
+  RSB_CUDA(cudaMemcpyToSymbol(rsb::jet::v2::g_timeline, &dev_ptr, sizeof(dev_ptr)));
+  return 0;
+}
+#endif

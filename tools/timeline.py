@@ -1,0 +1,40 @@
+"""Debug: per-phase clock64 timeline of jet2_kernel (build with RSB_NVCC_EXTRA=-DRSB_TIMELINE)."""
+import ctypes as C, sys
+import numpy as np
+sys.path.insert(0, ".")
+from radiosim_b200 import _lib as L
+from radiosim_b200.jets.packer import pack_jets
+lib = L.lib()
+n, size = 148 * 8, 256
+np.random.seed(1)
+b = pack_jets(n, size, (3, 10), "normalize")
+d_p, d_z = L.dev_from(b.params), L.dev_from(b.zoom_pad)
+d_img = L.DeviceBuffer(n * size * size * 4); d_m = L.DeviceBuffer(n * 4); d_k = L.DeviceBuffer(n * 8)
+tl = L.DeviceBuffer(n * 2 * 16 * 8)
+L.check(lib.rsb_memset(tl.ptr, 0, tl.nbytes, None))
+lib.rsb_debug_set_timeline.argtypes = [C.c_void_p]
+for rep in range(2):
+    L.check(lib.rsb_debug_set_timeline(tl.ptr))
+    L.check(lib.rsb_jet_render(d_p.ptr, d_z.ptr, n, 19, size, 1, d_img.ptr, d_m.ptr, d_k.ptr, None, 0, None))
+    L.device_sync()
+t = tl.download((n, 2, 16), np.int64)
+zoom = b.zoom_pad >= 0
+names = ["A->tiles done (this warp)", "->C (cluster sync / exch)", "->table built", "->H pass done (warp)", "->F barrier", "->halo", "->V pass done", "->best exch", "->stores done"]
+for label, sel in [("zoom", zoom), ("plain", ~zoom)]:
+    tt = t[sel]
+    print(label, "images", sel.sum())
+    if label == "zoom":
+        idx = [0,1,2,3,4,5,6,7,8,9]
+    else:
+        idx = [0,1,2,9]
+    for a_, b_ in zip(idx[:-1], idx[1:]):
+        d = (tt[:, :, b_] - tt[:, :, a_]).astype(np.float64)
+        print(f"  stamp {a_}->{b_}: mean {d.mean():9.0f}  p90 {np.percentile(d,90):9.0f}  rank0 {d[:,0].mean():9.0f} rank1 {d[:,1].mean():9.0f}")
+    d = (tt[:, :, 9] - tt[:, :, 0]).astype(np.float64)
+    print(f"  total per image: mean {d.mean():.0f}")
+# gap between images on the same CTA: next image's stamp0 - this image's stamp9
+ncl = 74
+gaps = []
+for i in range(n - ncl):
+    gaps.append(t[i + ncl, 0, 0] - t[i, 0, 9])
+print("gap stamp9 -> next stamp0 (barrier A wait etc):", np.mean(gaps))
