@@ -43,7 +43,8 @@ constexpr int kTileRows = 8;
 constexpr int kTileCols = 64;   // 2 columns per lane
 constexpr int kMaxBand = 128;   // rows per CTA band (V-pass results live in registers)
 constexpr int kRowsPerWarp = kMaxBand / kWarps;
-constexpr int kMaxGroups = 2 * kMaxBand / kTileRows;  // row groups of the WHOLE image
+constexpr int kMaxGroups = kMaxBand / kTileRows;
+constexpr int kMaxTiles = kMaxGroups * 4;  // 64-column tiles of a band (size <= 256)
 
 struct __align__(16) Fixed2 {
   double params[3][kMaxSlots * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
@@ -60,6 +61,7 @@ struct __align__(16) Fixed2 {
   int next_row;
   int foot_lo, foot_hi;             // output coordinates with a non-zero tap
   float delta[2];
+  unsigned char tile_order[kMaxTiles];  // tiles sorted by distance from the image centre
 };
 
 // one slot's float64 value at a raw pixel, operation order of gauss.py:77-88
@@ -320,13 +322,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     peer_xbar = cluster_map(smem_u32(&sm.xbar[0]), (uint32_t)(rank ^ 1));
     peer_raw = cluster_map(smem_u32(raw), (uint32_t)(rank ^ 1));
   }
-  float* peer_raw_g = raw;     // generic pointers into the peer CTA (remote tile stores)
-  Fixed2* peer_g = &sm;
-  if constexpr (kCluster > 1) {
-    cg::cluster_group cluster = cg::this_cluster();
-    peer_raw_g = cluster.map_shared_rank(raw, rank ^ 1);
-    peer_g = cluster.map_shared_rank(&sm, rank ^ 1);
-  }
   int xuse[3] = {0, 0, 0};  // uses so far of each exchange mbarrier (same in both CTAs)
   // swap one 64-bit value with the peer CTA (all threads call; value is CTA-uniform)
   auto exchange = [&](int kind, unsigned long long mine) -> unsigned long long {
@@ -347,12 +342,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
   const int strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
   const int tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
-  // phase-1 tiles cover the WHOLE image and are dealt alternately to the CTAs of the cluster
-  // (a one-sided jet would otherwise leave one band's CTA idle); a tile of the peer's band is
-  // written into the peer's shared memory.
-  const int ngroups_all = (N + kTileRows - 1) / kTileRows;
-  const int ntiles_all = ngroups_all * tcols;
-  const int ntiles = (ntiles_all - rank + kCluster - 1) / kCluster;
+  const int ntiles = ((H + kTileRows - 1) / kTileRows) * tcols;
   const bool vec = (N & 3) == 0;
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
@@ -371,6 +361,19 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     sm.next_tile = 0;
     sm.next_row = 0;
   }
+  // tile visiting order: by distance of the tile centre from the image centre, so that the
+  // heavy central tiles are dealt first and the dynamic schedule ends on light ones
+  for (int t = tid; t < ntiles; t += kThreads) {
+    auto key = [&](int u) {
+      const int gg = u / tcols, cc = u - gg * tcols;
+      const int dy = 2 * (R0 + gg * kTileRows) + kTileRows - N, dx = 2 * cc * kTileCols + kTileCols - N;
+      return (dy * dy + dx * dx) * 256 + u;  // unique
+    };
+    const int mykey = key(t);
+    int pos = 0;
+    for (int u = 0; u < ntiles; ++u) pos += key(u) < mykey;
+    sm.tile_order[pos] = (unsigned char)t;
+  }
   __syncthreads();
   auto prefetch = [&](int image, int pb) {  // one thread: parameter block -> params[pb]
     fence_proxy_async();
@@ -383,7 +386,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   }
   if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
-    build_coefs2(sm, 0, sm.params[0], slots, N, 0, N, lane);
+    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane);
   }
   // the peer CTA is resident and its mbarriers are initialised before any st.async
   if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -419,7 +422,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       // next image's coefficients and culling spans, hidden behind this image's phase 1
       const int nb = (it + 1) % 3;
       mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
-      build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, 0, N, lane);
+      build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane);
     }
     if (warp == 1) {
       // previous image's labels, then its parameter buffer is free for image it+2
@@ -445,15 +448,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (lane == 0) t = atomicAdd(&sm.next_tile, 1);
       t = __shfl_sync(0xffffffffu, t, 0);
       if (t >= ntiles) break;
-      const int ta = t * kCluster + rank;  // tile of the whole image, heaviest (central) rows first
-      const int jg = __float2int_rz(((float)ta + 0.5f) * inv_tcols), tc = ta - jg * tcols;
-      const int gc = (ngroups_all + 1) >> 1;
-      const int g = (jg & 1) ? gc + (jg >> 1) : gc - 1 - (jg >> 1);
-      const int r0 = g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
-      const bool mine = (kCluster == 1) || (r0 >= R0 && r0 < R0 + H);
-      float* dst = mine ? raw + (size_t)(r0 - base) * pitch
-                        : peer_raw_g + (size_t)(r0 - (rank == 0 ? H - 1 : 0)) * pitch;
-      const int rend = min(N, r0 + kTileRows);  // rows of this tile that exist
+      const int ta = sm.tile_order[t];  // central (heavy) tiles first, light corners last
+      const int g = __float2int_rz(((float)ta + 0.5f) * inv_tcols), tc = ta - g * tcols;
+      const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
+      float* dst = raw + (size_t)(r0 - base) * pitch;
+      const int rend = min(R0 + H, r0 + kTileRows);  // rows of this tile that exist
       const float r0f = (float)r0, c0f = (float)c0;
       f2 acc2[kTileRows];  // two adjacent pixels per row, packed (FFMA2)
 #pragma unroll
@@ -558,12 +557,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       }
       __syncthreads();
       image_best = sm.lbest;
-      if constexpr (kCluster > 1) {
-        // one cluster barrier per image: the peer's tiles have landed in my band, and the
-        // two partial arg-max keys are swapped by plain remote stores ordered by it
-        if (tid == 0) peer_g->xval[1][buf] = image_best;
-        cg::this_cluster().sync();  // (C') phase 1 done everywhere
-        const unsigned long long theirs = sm.xval[1][buf];
+      if (normalize) {
+        const unsigned long long theirs = exchange(2, image_best);
         image_best = theirs > image_best ? theirs : image_best;
       }
       RSB_STAMP(2);
@@ -583,11 +578,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (lane == 0 && my_margin < N) atomicMin(&sm.lmargin, my_margin);
       __syncthreads();
       margin = sm.lmargin;
-      if constexpr (kCluster > 1) {
-        if (tid == 0) peer_g->xval[0][buf] = (unsigned long long)(unsigned)margin;
-        cg::this_cluster().sync();  // (C) phase 1 done everywhere, the peer's tiles have landed
-        margin = min(margin, (int)sm.xval[0][buf]);
-      }
+      margin = min(margin, (int)exchange(0, (unsigned long long)(unsigned)margin));
       RSB_STAMP(2);
       if (margin >= N) margin = 0;  // empty mask -> idx 0 (argmax of an all-false array)
       if (tid == 0) {
@@ -628,6 +619,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       const int flo = sm.foot_lo, fhi = sm.foot_hi;  // empty footprint: flo = N, fhi = -1
 
 
+      int dbg_rows_out = 0;
       // H pass, in place: row r of raw becomes row r of T.  Column taps stay in registers,
       // rows are pulled from a shared counter (warp 0 joins late).
       {
@@ -635,25 +627,31 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         bool act[NS];
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
-          const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
+          // lane <-> ADJACENT columns (c = strip + 32 j + lane): the gathers of a warp touch
+          // consecutive words (composite stride <= 2), not every 4th
+          const int sc0 = s * kStrip;
           act[s] = (s < strips) && sc0 <= fhi && sc0 + kStrip - 1 >= flo;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const int c = min(c0 + j, npad - 1);
+            const int cj = sc0 + 32 * j + lane;
+            const int c = min(cj, npad - 1);
 #pragma unroll
             for (int k = 0; k < 3; ++k)
-              ct[s][j].w[k] = (act[s] && c0 + j < N) ? tab_w[k * npad + c] : 0.f;
+              ct[s][j].w[k] = (act[s] && cj < N) ? tab_w[k * npad + c] : 0.f;
             ct[s][j].i = act[s] ? tab_i[c] : 0;
           }
         }
         const int rlo = max(R0, margin), rhi = min(R0 + H, N - margin);
+        RSB_STAMP(10);
+        int dbg_rows = 0;
         for (;;) {
           int r = 0;
           if (lane == 0) r = atomicAdd(&sm.next_row, 1);
           r = __shfl_sync(0xffffffffu, r, 0) + rlo;
           if (r >= rhi) break;
+          ++dbg_rows;
           float* row = raw + (size_t)(r - base) * pitch;
-          float4 res[NS];
+          float res[NS][4];
 #pragma unroll
           for (int s = 0; s < NS; ++s) {
             float o[4] = {0.f, 0.f, 0.f, 0.f};
@@ -666,16 +664,26 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
                 o[j] = fmaf(ct[s][j].w[2], src[2], o[j]);
               }
             }
-            res[s] = make_float4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) res[s][j] = o[j];
           }
           __syncwarp();
+          dbg_rows_out = dbg_rows;
 #pragma unroll
           for (int s = 0; s < NS; ++s) {
-            const int c0 = s * kStrip + 4 * lane;
-            if (act[s] && c0 < N) *reinterpret_cast<float4*>(row + c0) = res[s];
+            if (act[s]) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int cj = s * kStrip + 32 * j + lane;
+                if (cj < N) row[cj] = res[s][j];
+              }
+            }
           }
         }
       }
+#ifdef RSB_TIMELINE
+      if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 16 + 11] = dbg_rows_out;
+#endif
       RSB_STAMP(4);
       __syncthreads();  // (F) T complete in this band
       RSB_STAMP(5);
@@ -825,8 +833,7 @@ bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
     *smem_bytes = v2_bytes(size, 1);
     return true;
   }
-  // two bands of whole 8-row tile groups
-  if ((size % 16) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
+  if ((size & 1) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
     *cluster = 2;
     *smem_bytes = v2_bytes(size, 2);
     return true;

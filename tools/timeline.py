@@ -32,6 +32,9 @@ for label, sel in [("zoom", zoom), ("plain", ~zoom)]:
         print(f"  stamp {a_}->{b_}: mean {d.mean():9.0f}  p90 {np.percentile(d,90):9.0f}  rank0 {d[:,0].mean():9.0f} rank1 {d[:,1].mean():9.0f}")
     d = (tt[:, :, 9] - tt[:, :, 0]).astype(np.float64)
     print(f"  total per image: mean {d.mean():.0f}")
+tz=t[zoom]
+d=(tz[:,:,10]-tz[:,:,3]).astype(float); print("H: taps load", d.mean())
+d=(tz[:,:,4]-tz[:,:,10]).astype(float); print("H: row loop", d.mean(), "rows by this warp", tz[:,:,11].mean(), "margin mean", b.zoom_pad[zoom].mean())
 # gap between images on the same CTA: next image's stamp0 - this image's stamp9
 ncl = 74
 gaps = []
