@@ -32,18 +32,22 @@ namespace v2 {
 
 #ifdef RSB_TIMELINE
 __device__ long long* g_timeline = nullptr;  // [image][rank][16] clock64 stamps (debug builds)
+#define RSB_STAMP_T(k, t) do { if (g_timeline && tid == (t)) g_timeline[((size_t)img * 2 + rank) * 16 + (k)] = clock64(); } while (0)
 #define RSB_STAMP(k) do { if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 16 + (k)] = clock64(); } while (0)
 #else
 #define RSB_STAMP(k) do {} while (0)
+#define RSB_STAMP_T(k, t) do {} while (0)
 #endif
 
-constexpr int kThreads = 512;
-constexpr int kWarps = kThreads / 32;
+constexpr int kWorkers = 512;             // threads that render
+constexpr int kWarps = kWorkers / 32;
+constexpr int kThreads = kWorkers;
 constexpr int kTileRows = 8;
 constexpr int kTileCols = 64;   // 2 columns per lane
 constexpr int kMaxBand = 128;   // rows per CTA band (V-pass results live in registers)
 constexpr int kRowsPerWarp = kMaxBand / kWarps;
 constexpr int kMaxGroups = kMaxBand / kTileRows;
+constexpr int kMaxCand = 64;
 constexpr int kMaxTiles = kMaxGroups * 4;  // 64-column tiles of a band (size <= 256)
 
 struct __align__(16) Fixed2 {
@@ -61,6 +65,10 @@ struct __align__(16) Fixed2 {
   int next_row;
   int foot_lo, foot_hi;             // output coordinates with a non-zero tap
   float delta[2];
+  int dlo[2];                       // no pixel closer than this to the border exceeds 0.01
+  struct LabelReq { unsigned long long best; int img, pb, margin, zpad; } label[2];  // [image parity]
+  int ncand;                        // borderline pixels awaiting a float64 verdict
+  int cand[kMaxCand];               // r << 16 | c
   unsigned char tile_order[kMaxTiles];  // tiles sorted by distance from the image centre
 };
 
@@ -115,7 +123,7 @@ __device__ __forceinline__ void store_out4(char* out_row, bool f64, int c0, int 
 // concave in dr, so its maximum over the range is the ellipse's rightmost point if that
 // row lies in the range, else the larger end value (mirror image for cl).
 __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
-                                    int H, int lane) {
+                                    int H, int lane, bool zoom) {
   float amax = 0.f;
   for (int k = lane; k < slots; k += 32) amax = fmaxf(amax, fabsf((float)P[k * 6]));
   amax = warp_max(amax);
@@ -198,9 +206,81 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
     }
     base += __popc(mask);
   }
+  // Zoom images only use the crop [margin, N-margin)^2 of the raw image, and margin >= dlo,
+  // where dlo is the smallest border distance d at which an UPPER BOUND of the image over
+  // the frame {border distance <= d} exceeds the 0.01 threshold.  Bound: sum over slots of
+  // the slot's maximum over the frame = amp if its centre lies in the frame, else
+  // amp * exp(-q/2) with q the smallest Mahalanobis distance to the four frame lines.
+  int dlo = 0;
+  if (zoom) {
+    // per-slot constants (slots k = lane and lane + 32), float32 with a safety margin
+    float ka[2], kx[2], ky[2], cx[2], cy[2];
+    bool certified = false, all_nonneg = true;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = lane + 32 * h;
+      ka[h] = 0.f; kx[h] = ky[h] = 0.f; cx[h] = cy[h] = 0.f;
+      if (k < slots && P[k * 6] != 0.0) {
+        const double* p = P + k * 6;
+        double sr, cr;
+        sincos(p[5], &sr, &cr);
+        const double iu = 1.0 / (p[4] * p[4]), iv = 1.0 / (p[3] * p[3]);
+        const double mrr = cr * cr * iu + sr * sr * iv, mcc = sr * sr * iu + cr * cr * iv;
+        const double mrc = sr * cr * (iv - iu);
+        const double det = mrr * mcc - mrc * mrc;
+        ka[h] = (float)fabs(p[0]) * 1.0001f;
+        kx[h] = (float)(det / mrr) * 0.9999f * 0.72134752f;  // * log2(e)/2
+        ky[h] = (float)(det / mcc) * 0.9999f * 0.72134752f;
+        cx[h] = (float)p[1];
+        cy[h] = (float)p[2];
+        if (p[0] < 0.0) all_nonneg = false;
+        // the pixel nearest to the centre is at most half a pixel away in each coordinate:
+        // this slot alone lifts it above the threshold -> the > 0.01 mask is not empty
+        const double qmax = 0.25 * (mrr + mcc + 2.0 * fabs(mrc));
+        if (p[0] * exp(-0.5 * qmax) > 0.0101 && p[1] >= 0.0 && p[1] <= N - 1.0 && p[2] >= 0.0 &&
+            p[2] <= N - 1.0)
+          certified = true;
+      }
+    }
+    certified = __any_sync(0xffffffffu, certified) && __all_sync(0xffffffffu, all_nonneg) &&
+                slots <= 64;
+    auto frame_bound = [&](int d) -> float {
+      const float lo = (float)d, hi = (float)(N - 1 - d);
+      float u = 0.f;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if (ka[h] == 0.f) continue;
+        float v = ka[h];
+        if (!(cx[h] <= lo || cx[h] >= hi || cy[h] <= lo || cy[h] >= hi)) {
+          const float dc0 = lo - cx[h], dc1 = hi - cx[h], dr0 = lo - cy[h], dr1 = hi - cy[h];
+          const float q = fminf(fminf(dc0 * dc0, dc1 * dc1) * kx[h], fminf(dr0 * dr0, dr1 * dr1) * ky[h]);
+          v *= ex2(-q);
+        }
+        u += v;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+      return u;
+    };
+    const float limit = 0.00999f;
+    // without the certificate an empty mask (margin := 0, whole image used) cannot be ruled out
+    if (certified && frame_bound(0) <= limit) {
+      int a_ = 0, b_ = (N - 1) / 2;
+      if (frame_bound(b_) <= limit) {
+        a_ = -1;  // cannot happen with a certificate; stay safe
+      } else {
+        while (b_ - a_ > 1) {
+          const int mid = (a_ + b_) >> 1;
+          if (frame_bound(mid) <= limit) a_ = mid; else b_ = mid;
+        }
+      }
+      dlo = a_ + 1;  // frames 0..a_ hold nothing above the threshold
+    }
+  }
   if (lane == 0) {
     sm.nlive[cb] = base;
     sm.delta[cb] = 2e-6f * fmaxf(1.f, amax);
+    sm.dlo[cb] = dlo;
   }
 }
 
@@ -281,7 +361,7 @@ __device__ inline Tap3 merge_taps(const Taps64& t, int N) {
     if (t.w[k] != 0.0) lo = min(lo, t.i[k]);
   double w0 = 0.0, w1 = 0.0, w2 = 0.0;
   if (lo == 0x7fffffff) {
-    lo = 0;
+    lo = max((N >> 1) - 1, 0);  // no tap: point at the image centre, which is always rendered
   } else {
     lo = max(min(lo, N - 3), 0);
 #pragma unroll
@@ -347,6 +427,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
   const size_t esz = f64 ? 8 : 4;
+  // float32 output with contiguous rows: the finished band is staged in shared memory (over
+  // the raw image) and leaves through one bulk async copy
+  const bool bulk = false && !f64 && vec && pitch == N;  // measured: TMA drains shared memory no faster than STG (~30 B/clk/SM)
 
   if (tid == 0) {
     mbar_init(&sm.bar[0], 1);
@@ -363,7 +446,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   }
   // tile visiting order: by distance of the tile centre from the image centre, so that the
   // heavy central tiles are dealt first and the dynamic schedule ends on light ones
-  for (int t = tid; t < ntiles; t += kThreads) {
+  for (int t = tid; t < ntiles; t += kWorkers) {
     auto key = [&](int u) {
       const int gg = u / tcols, cc = u - gg * tcols;
       const int dy = 2 * (R0 + gg * kTileRows) + kTileRows - N, dx = 2 * cc * kTileCols + kTileCols - N;
@@ -386,24 +469,25 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   }
   if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
-    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane);
+    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0);
   }
   // the peer CTA is resident and its mbarriers are initialised before any st.async
   if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
   int zpad_next = (cid < a.n) ? a.zoom_pad[cid] : -1;
 
-  // label job of the previous image (warp 1 of rank 0 runs it during the next phase 1)
-  bool prev_valid = false, prev_zoom = false;
-  int prev_img = 0, prev_pb = 0, prev_margin = 0, prev_zpad = 0;
-  unsigned long long prev_best = 0ull;
-  auto label_job = [&]() {
+  // Two warps start each image with a side job before they join the tile queue: warp 0 builds
+  // the NEXT image's coefficients and culling spans, warp 1 turns the PREVIOUS image's arg-max
+  // into the float64 peak label.  (Dedicated helper warps were tried: no gain, more spills.)
+  constexpr int kCoefWarp = 0, kLabelWarp = 1;
+  auto worker_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(kWorkers) : "memory"); };
+  auto label_job = [&](int par) {
+    const Fixed2::LabelReq q = sm.label[par];
     double peak = 1.0;
     if (normalize)
-      peak = peak64(sm.pix64, sm.params[prev_pb], slots, N, prev_zoom, prev_zpad, prev_margin,
-                    prev_best, lane);
+      peak = peak64(sm.pix64, sm.params[q.pb], slots, N, q.zpad >= 0, q.zpad, q.margin, q.best, lane);
     if (lane == 0) {
-      a.margin[prev_img] = prev_margin;
-      a.peak[prev_img] = peak;
+      a.margin[q.img] = q.margin;
+      a.peak[q.img] = peak;
     }
   };
 
@@ -412,29 +496,38 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const int buf = it & 1;   // coefficient / exchange-slot parity
     const int pb = it % 3;    // parameter buffer
     mbar_wait(&sm.bar[pb], (it / 3) & 1);
+    if (tid == 0) bulk_wait_read();  // the previous image's band has left shared memory
     __syncthreads();  // (A) coef/span/nlive of this image visible; raw free for reuse
-    RSB_STAMP(0);
     if (tid == 0) {  // running reductions of this image (all reads of the previous values are behind A)
       sm.lbest = 0ull;
       sm.lmargin = N;
+      sm.ncand = 0;
     }
-    if (warp == 0 && img + nclusters < a.n) {
-      // next image's coefficients and culling spans, hidden behind this image's phase 1
-      const int nb = (it + 1) % 3;
-      mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
-      build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane);
+    __syncwarp();
+    {
+      if (warp == kCoefWarp) {
+        if (img + nclusters < a.n) {
+          const int nb = (it + 1) % 3;
+          mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
+          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane,
+                       a.zoom_pad[img + nclusters] >= 0);
+        }
+        RSB_STAMP_T(12, kCoefWarp * 32);
+      } else if (warp == kLabelWarp) {
+        // previous image's labels, then its parameter buffer is free for image it+2
+        if (rank == 0 && it > 0) label_job(buf ^ 1);
+        if (lane == 0 && img + 2 * nclusters < a.n) prefetch(img + 2 * nclusters, (it + 2) % 3);
+        RSB_STAMP_T(13, kLabelWarp * 32);
+      }
     }
-    if (warp == 1) {
-      // previous image's labels, then its parameter buffer is free for image it+2
-      if (rank == 0 && prev_valid) label_job();
-      if (lane == 0 && img + 2 * nclusters < a.n) prefetch(img + 2 * nclusters, (it + 2) % 3);
-    }
+    RSB_STAMP(0);
     const double* P = sm.params[pb];
     const int zpad = zpad_next;
     if (img + nclusters < a.n) zpad_next = a.zoom_pad[img + nclusters];  // latency hidden
     const bool zoom = zpad >= 0;
     const int nlive = sm.nlive[buf];
     const float thr = (float)kEdgeThr, delta = sm.delta[buf];
+    const int dlo = sm.dlo[buf];
     const Coef* coef = sm.coef[buf];
     const int (*span)[kMaxGroups] = sm.span[buf];
 
@@ -453,6 +546,13 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
       float* dst = raw + (size_t)(r0 - base) * pitch;
       const int rend = min(R0 + H, r0 + kTileRows);  // rows of this tile that exist
+      {
+        // every pixel of the tile closer than dlo to the border: never read, never above 0.01
+        const int rmid = min(max(N >> 1, r0), rend - 1), cmid = min(max(N >> 1, tc0), min(tc0 + kTileCols, N) - 1);
+        const int far = min(min(rmid, N - 1 - rmid), min(cmid, N - 1 - cmid));
+        // (two pixels of slack: zero-weight taps may touch the crop's neighbours)
+        if (zoom && far < dlo - 2) continue;
+      }
       const float r0f = (float)r0, c0f = (float)c0;
       f2 acc2[kTileRows];  // two adjacent pixels per row, packed (FFMA2)
 #pragma unroll
@@ -519,9 +619,15 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
                 const int c = c0 + j;
                 const int d = min(db, min(c, N - 1 - c));
                 if (c < N && d < my_margin && acc[i][j] > thr - delta) {
-                  bool above = acc[i][j] > thr;
-                  if (acc[i][j] < thr + delta) above = eval64(P, slots, r, c) > kEdgeThr;
-                  if (above) my_margin = d;
+                  if (acc[i][j] >= thr + delta) {
+                    my_margin = d;  // definitely above
+                  } else {
+                    // within float32 noise of the threshold: float64 decides, later and only
+                    // if it can still lower the margin
+                    const int slot = atomicAdd(&sm.ncand, 1);
+                    if (slot < kMaxCand) sm.cand[slot] = (r << 16) | c;
+                    else if (eval64(P, slots, r, c) > kEdgeThr) my_margin = d;
+                  }
                 }
               }
             }
@@ -555,7 +661,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         my_best = warp_max_u64(my_best);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
       }
-      __syncthreads();
+      worker_sync();
       image_best = sm.lbest;
       if (normalize) {
         const unsigned long long theirs = exchange(2, image_best);
@@ -565,18 +671,39 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (tid == 0) sm.next_tile = 0;
       const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
-      for (int e = tid; e < H * q4; e += kThreads) {
+      for (int e = tid; e < H * q4; e += kWorkers) {
         const int rl = e / q4, c0 = (e - rl * q4) << 2;
         const int r = R0 + rl;
         float4 v = *reinterpret_cast<const float4*>(raw + (size_t)(r - base) * pitch + c0);
         v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-        store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+        if (bulk) *reinterpret_cast<float4*>(raw + (size_t)(r - base) * pitch + c0) = v;
+        else store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
       }
     } else {
       // ------------- zoom branch ------------------------------------------------------
       my_margin = warp_min(my_margin);
       if (lane == 0 && my_margin < N) atomicMin(&sm.lmargin, my_margin);
-      __syncthreads();
+      worker_sync();
+      {
+        const int ncand = min(sm.ncand, kMaxCand);
+        if (ncand > 0) {  // CTA-uniform, rare
+          const int mdef = sm.lmargin;
+          worker_sync();
+          for (int q = warp; q < ncand; q += kWarps) {
+            const int rc = sm.cand[q], r = rc >> 16, c = rc & 0xffff;
+            const int d = min(min(r, N - 1 - r), min(c, N - 1 - c));
+            if (d < mdef) {
+              double s = 0.0;
+              for (int k0 = 0; k0 < slots; k0 += 32) {
+                const double t = (k0 + lane < slots) ? gauss64(P + 6 * (k0 + lane), r, c) : 0.0;
+                for (int l = 0; l < 32; ++l) s += __shfl_sync(0xffffffffu, t, l);  // slot order
+              }
+              if (lane == 0 && s > kEdgeThr) atomicMin(&sm.lmargin, d);
+            }
+          }
+          worker_sync();
+        }
+      }
       margin = sm.lmargin;
       margin = min(margin, (int)exchange(0, (unsigned long long)(unsigned)margin));
       RSB_STAMP(2);
@@ -587,12 +714,12 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         sm.foot_lo = N;
         sm.foot_hi = -1;
       }
-      __syncthreads();  // foot_* initialised before the atomics below
+      worker_sync();  // foot_* initialised before the atomics below
 
       // composite tap table (float64 math, float32 weights) + output footprint
       {
         int lo = N, hi = -1;
-        for (int d = tid; d < npad; d += kThreads) {
+        for (int d = tid; d < npad; d += kWorkers) {
           Tap3 m;
           m.w[0] = m.w[1] = m.w[2] = 0.f;
           m.i = 0;
@@ -614,7 +741,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           if (hi >= 0) atomicMax(&sm.foot_hi, hi);
         }
       }
-      __syncthreads();  // (D)
+      worker_sync();  // (D)
       RSB_STAMP(3);
       const int flo = sm.foot_lo, fhi = sm.foot_hi;  // empty footprint: flo = N, fhi = -1
 
@@ -638,37 +765,34 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
             for (int k = 0; k < 3; ++k)
               ct[s][j].w[k] = (act[s] && cj < N) ? tab_w[k * npad + c] : 0.f;
-            ct[s][j].i = act[s] ? tab_i[c] : 0;
+            ct[s][j].i = act[s] ? tab_i[c] : max((N >> 1) - 1, 0);
           }
         }
         const int rlo = max(R0, margin), rhi = min(R0 + H, N - margin);
         RSB_STAMP(10);
-        int dbg_rows = 0;
-        for (;;) {
-          int r = 0;
-          if (lane == 0) r = atomicAdd(&sm.next_row, 1);
-          r = __shfl_sync(0xffffffffu, r, 0) + rlo;
-          if (r >= rhi) break;
-          ++dbg_rows;
+        // rows are dealt statically; inactive strips carry zero weights and index 0, so the
+        // gathers need no branches (24 independent loads in flight per row)
+        for (int r = rlo + warp; r < rhi; r += kWarps) {
           float* row = raw + (size_t)(r - base) * pitch;
+          float v[NS][4][3];
+#pragma unroll
+          for (int s = 0; s < NS; ++s)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float* src = row + ct[s][j].i;
+              v[s][j][0] = src[0];
+              v[s][j][1] = src[1];
+              v[s][j][2] = src[2];
+            }
           float res[NS][4];
 #pragma unroll
-          for (int s = 0; s < NS; ++s) {
-            float o[4] = {0.f, 0.f, 0.f, 0.f};
-            if (act[s]) {
+          for (int s = 0; s < NS; ++s)
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float* src = row + ct[s][j].i;
-                o[j] = ct[s][j].w[0] * src[0];
-                o[j] = fmaf(ct[s][j].w[1], src[1], o[j]);
-                o[j] = fmaf(ct[s][j].w[2], src[2], o[j]);
-              }
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) res[s][j] = o[j];
-          }
+            for (int j = 0; j < 4; ++j)
+              res[s][j] = fmaf(ct[s][j].w[2], v[s][j][2],
+                               fmaf(ct[s][j].w[1], v[s][j][1], ct[s][j].w[0] * v[s][j][0]));
           __syncwarp();
-          dbg_rows_out = dbg_rows;
+          ++dbg_rows_out;
 #pragma unroll
           for (int s = 0; s < NS; ++s) {
             if (act[s]) {
@@ -685,13 +809,13 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 16 + 11] = dbg_rows_out;
 #endif
       RSB_STAMP(4);
-      __syncthreads();  // (F) T complete in this band
+      worker_sync();  // (F) T complete in this band
       RSB_STAMP(5);
       if constexpr (kCluster > 1) {
         // halo: my boundary row of T goes into the peer's halo slot
         const int src = (rank == 0) ? (H - 1) : 1;  // local index of absolute row H-1 / H
         const int dst = (rank == 0) ? 0 : H;        // peer's halo slot
-        for (int e = tid; e < (pitch >> 2); e += kThreads)
+        for (int e = tid; e < (pitch >> 2); e += kWorkers)
           st_async_v4(peer_raw + (uint32_t)(dst * pitch + 4 * e) * 4u,
                       reinterpret_cast<const float4*>(raw + (size_t)src * pitch)[e], peer_xbar + 8u);
         if (tid == 0) mbar_expect_tx(&sm.xbar[1], (uint32_t)pitch * 4u);
@@ -752,13 +876,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (normalize) {
         my_best = warp_max_u64(my_best);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
-        __syncthreads();  // (G) this band's arg-max complete
+        worker_sync();  // (G) this band's arg-max complete
         image_best = sm.lbest;
         const unsigned long long theirs = exchange(2, image_best);
         image_best = theirs > image_best ? theirs : image_best;
         inv = 1.f / __uint_as_float((unsigned)(image_best >> 32));
       }
       RSB_STAMP(8);
+      if (bulk && !normalize) worker_sync();  // every V-pass read of raw is done
 #pragma unroll
       for (int i = 0; i < kRowsPerWarp; ++i) {
         const int r = R0 + warp + i * kWarps;
@@ -769,22 +894,29 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           if (s >= strips || c0 >= N) continue;
           float4 v = res[i][s];
           v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-          store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+          if (bulk) *reinterpret_cast<float4*>(raw + (size_t)(r - base) * pitch + c0) = v;
+          else store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
         }
       }
     }
+    if (bulk) {
+      fence_proxy_async();  // my shared-memory writes -> visible to the async (TMA) proxy
+      worker_sync();
+      if (tid == 0)
+        bulk_s2g(out + (size_t)R0 * N * 4, raw + (size_t)(R0 - base) * pitch, (uint32_t)(H * N * 4));
+    }
 
     RSB_STAMP(9);
-    // this image's labels are produced during the next image's phase 1
-    prev_valid = true;
-    prev_img = img;
-    prev_pb = pb;
-    prev_margin = margin;
-    prev_zpad = zpad;
-    prev_zoom = zoom;
-    prev_best = image_best;
+    // this image's labels are produced by the label warp during the next image
+    if (tid == 0) {
+      Fixed2::LabelReq q;
+      q.best = image_best; q.img = img; q.pb = pb; q.margin = margin; q.zpad = zpad;
+      sm.label[buf] = q;
+    }
   }
-  if (rank == 0 && warp == 1 && prev_valid) label_job();
+  if (tid == 0) bulk_wait_read();
+  __syncthreads();
+  if (rank == 0 && warp == kLabelWarp && it > 0) label_job((it - 1) & 1);
   if constexpr (kCluster > 1) cg::this_cluster().sync();  // no CTA exits while its smem is in use
 }
 

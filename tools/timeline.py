@@ -35,6 +35,8 @@ for label, sel in [("zoom", zoom), ("plain", ~zoom)]:
 tz=t[zoom]
 d=(tz[:,:,10]-tz[:,:,3]).astype(float); print("H: taps load", d.mean())
 d=(tz[:,:,4]-tz[:,:,10]).astype(float); print("H: row loop", d.mean(), "rows by this warp", tz[:,:,11].mean(), "margin mean", b.zoom_pad[zoom].mean())
+ok=(t[:,:,12]>0)&(t[:,:,13]>0)
+print("warp0 coef build", (t[:,:,12]-t[:,:,0])[ok].mean(), "warp1 label job", (t[:,:,13]-t[:,:,0])[ok[:,0],0].mean())
 # gap between images on the same CTA: next image's stamp0 - this image's stamp9
 ncl = 74
 gaps = []
