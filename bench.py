@@ -42,6 +42,7 @@ COMPS = (3, 10)
 SLOTS = 2 * COMPS[1] - 1
 METRIC = "images/sec (whole box) for 256x256 jet batches"
 UNIT = "images/s"
+NCU_DRAM_BYTES_PER_IMAGE = 250230  # measured, see profiles/README.md
 WORKLOAD = "C5: jet 256x256, default jet params (num_jet_components [3,10], scaling normalize)"
 
 
@@ -325,8 +326,14 @@ def run_cuda(args):
             "gpu_launches": launches_all,
             "roofline": {
                 "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
-                "kernel": "rsb::jet::jet_kernel", "algorithmic_bytes_per_image": bytes_per_img,
+                "frac": achieved_gbs / hbm_peak,
+                # dram__bytes_read+write of one launch from the ncu --set full capture, scaled to
+                # this launch's batch (profiles/r01_jet2_kernel_ncu_full_raw.csv: 1.0249 GB / 4096 jets)
+                "traffic": NCU_DRAM_BYTES_PER_IMAGE * batch, "traffic_unit": "bytes per launch",
+                "traffic_source": "ncu --set full, 4096-jet launch, scaled by batch",
+                "peak_source": peak_src,
+                "kernel": "rsb::jet::v2::jet2_kernel<2,2>", "algorithmic_bytes_per_image": bytes_per_img,
+                "algorithmic_bytes_per_launch": bytes_per_img * batch,
                 "governing": "sfu",
                 "sfu_achieved_ex2_per_s": sfu_achieved, "sfu_peak_ex2_per_s": sfu.value,
                 "sfu_frac": sfu_achieved / sfu.value if sfu.value else None,
