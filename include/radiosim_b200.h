@@ -113,6 +113,31 @@ int rsb_jet_render_host(const double* params_host, const int32_t* zoom_pad_host,
                         int slots, int size, unsigned flags, void* out_img_host,
                         int32_t* out_margin_host, double* out_peak_host);
 
+/* ------------------------------------------------------------------- survey */
+/* Replaces the pixel work of create_survey (src/radiosim/survey/survey.py:49-122): every
+ * gaussian / point source (survey.py:79-106) is a row [amp, x, y, sx, sy, rot] as handed to
+ * twodgaussian (src/radiosim/utils/gauss.py:50-97); sub-jets (survey.py:54-76) are rendered
+ * beforehand with rsb_jet_render into one packed float32 buffer and pasted here with the
+ * reference's clipping; then the per-image max-normalisation and background plane
+ * (survey.py:109-122).
+ *
+ *  src_params_dev [total_sources][6] float64, grouped per image: class-1 (gaussian) rows,
+ *                 then class-2 (point) rows
+ *  src_offs_dev   [n][3] int32: first class-1 row, first class-2 row, end row of image i
+ *  jet_rects_dev  [jet_offs[n]] records {int64 pix; int32 size, row0, col0, pad}: offset of the
+ *                 sub-jet's first pixel in jet_pix_dev, its edge, and the image position of
+ *                 its pixel (0,0): row0 = floor(x - size/2), col0 = floor(y - size/2)
+ *                 (survey.py:61-64; may be negative)
+ *  jet_offs_dev   [n + 1] int32: sub-jets of image i are jet_offs[i] .. jet_offs[i+1]-1
+ *  out_x_dev      [n][size][size], out_y_dev [n][4][size][size]: float32, or float64 with
+ *                 RSB_JET_OUT_F64 (planes: jets, gaussians, points, background)
+ *  workspace_dev  >= rsb_survey_workspace_bytes() bytes of device scratch */
+int rsb_survey_workspace_bytes(int n, int size, int total_sources, size_t* bytes);
+int rsb_survey_render(const double* src_params_dev, const int32_t* src_offs_dev,
+                      int total_sources, const void* jet_rects_dev, const int32_t* jet_offs_dev,
+                      const float* jet_pix_dev, int n, int size, unsigned flags, void* out_x_dev,
+                      void* out_y_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
 /* rsb_jet_render without any allocation, for hosts that cannot call cudaMalloc once
  * they are running: a plugin inside a process whose framework has already reserved the
  * device for its own memory pool, or a service with a device-memory budget fixed at

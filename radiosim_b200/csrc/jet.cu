@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) jet_kernel(const Args a)
   const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
   const int strips = (N + kStrip - 1) / kStrip;
   const int items = N * strips;
-  const bool vec = (N & 3) == 0;
+  const bool vec = (N & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
 
   if (tid == 0) {
     mbar_init(&sm.bar[0], 1);

@@ -423,7 +423,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const int strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
   const int tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
   const int ntiles = ((H + kTileRows - 1) / kTileRows) * tcols;
-  const bool vec = (N & 3) == 0;
+  const bool vec = (N & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
   const size_t esz = f64 ? 8 : 4;

@@ -1,0 +1,68 @@
+"""GPU parity tests of the survey path (tiled splat + sub-jet paste + normalise)."""
+
+import os
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5  # of the (normalised) image peak
+
+
+def _conf(num_sources, dist=(2, 1, 2), scale=True):
+    return SimpleNamespace(
+        jet=SimpleNamespace(training_type="list", scaling="normalize", num_jet_components=[3, 10]),
+        survey=SimpleNamespace(num_sources=num_sources, class_distribution=list(dist), scale_sources=scale))
+
+
+@pytest.mark.parametrize("name", ["survey_128", "survey_160"])
+def test_create_survey_matches_reference_golden(golden_dir, name):
+    from radiosim_b200.survey import create_survey
+
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    n, size = int(g["n"]), int(g["size"])
+    np.random.seed(int(g["seed"]))
+    x, y = create_survey(np.broadcast_to(np.zeros(1), (n, 3, size, size)), _conf(int(g["num_sources"])))
+    assert np.random.rand() == float(g["next_rand"])  # RNG stream stayed aligned
+    assert x.shape == g["x"].shape and y.shape == g["y"].shape and x.dtype == np.float64
+    assert np.abs(x - g["x"]).max() <= TOL
+    assert np.abs(y - g["y"]).max() <= TOL
+
+
+@pytest.mark.parametrize("size,n,ns,seed,dist", [(128, 3, 20, 5, (2, 1, 2)), (200, 2, 40, 6, (1, 3, 3)),
+                                                 (256, 2, 60, 7, (2, 1, 2)), (300, 1, 30, 8, (0, 1, 1))])
+def test_survey_matches_oracle(size, n, ns, seed, dist):
+    from oracle import survey as osur
+    from radiosim_b200.survey import create_survey
+
+    np.random.seed(seed)
+    ox, oy = osur.create_survey((n, 3, size, size), ns, dist, True)
+    np.random.seed(seed)
+    x, y = create_survey(np.broadcast_to(np.zeros(1), (n, 3, size, size)), _conf(ns, dist))
+    assert np.abs(x - ox).max() <= TOL
+    assert np.abs(y - oy).max() <= TOL
+    assert np.abs(x.reshape(n, -1).max(axis=1) - 1.0).max() <= 2e-6
+
+
+def test_survey_large_grid_properties():
+    """BASELINE config 4 size (1024^2, thousands of sources): oracle-free properties."""
+    from radiosim_b200.survey.survey import pack_survey, render_survey
+
+    np.random.seed(9)
+    b = pack_survey(1, 1024, 2000, (0, 1, 2), True)  # no sub-jets: pure tiled splat
+    x, y = render_survey(b, f64=False)
+    assert np.isfinite(x).all() and (x >= 0).all()
+    assert abs(float(x.max()) - 1.0) <= 2e-6
+    assert np.abs(y[:, :3].sum(axis=1) - x[:, 0]).max() <= 1e-5   # planes add up to the image
+    assert np.abs(y[:, 3] - (1 - x[:, 0])).max() <= 1e-6          # background plane
+    # a lone source reproduces twodgaussian
+    from oracle.gauss import twodgaussian
+    from radiosim_b200.survey.survey import SurveyBatch
+
+    p = np.array([[0.8, 300.25, 700.5, 30.0, 22.0, 0.6]])
+    one = SurveyBatch(1024, 1, p, np.array([[0, 1, 1]], np.int32), [], np.zeros(0, np.int64),
+                      np.zeros(0, np.int64), np.zeros(0, np.int64))
+    x1, _ = render_survey(one, f64=False)
+    ref = twodgaussian(p[0], 1024)
+    assert np.abs(x1[0, 0] - ref / ref.max()).max() <= TOL
