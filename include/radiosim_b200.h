@@ -138,6 +138,35 @@ int rsb_survey_render(const double* src_params_dev, const int32_t* src_offs_dev,
                       const float* jet_pix_dev, int n, int size, unsigned flags, void* out_x_dev,
                       void* out_y_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------- ppdisk */
+/* Replaces the tensor work of create_proto (src/radiosim/ppdisks/ppdisks.py:95-185) on the
+ * reference's fixed 900 x 900 grid.  The host replays the RNG chain and packs
+ *
+ *  comps_dev  [n_comps] records of 48 bytes:
+ *             {float ca, sa;           float32(cos/sin(deg2rad(alpha)))       (:225-233)
+ *              float a2_in, b2_in;     float32(a^2), float32(b^2) of the inner ellipse of a
+ *                                      ring, a2_in <= 0 for the core          (:269, :305)
+ *              float a2_out, b2_out;   the (outer) ellipse
+ *              float scale;            _get_scale                              (:477-483)
+ *              int32 sigma;            smoothing width                         (:135, :380-394)
+ *              int32 image; int32 pad[3];}
+ *  images_dev [n_images] records of 32 bytes:
+ *             {int32 comp0, ncomp;     components of the image, core first
+ *              int32 lo, hi;           crop [lo, hi) of the 900 grid           (:154-161)
+ *              int32 new_size;         resize target                           (:166-171)
+ *              int32 pad[3];}
+ *  htab_dev   [17][900] float32: htab[s][t] = g_s(t - 449.5) / sum_t g_s(t - 449.5), the 1-D
+ *             factor of astropy's Gaussian2DKernel(s, s, x_size=900, y_size=900)  (:446-450)
+ *  out_dev    [n_images][img_size][img_size] float32 (the reference's output dtype)
+ *
+ * rsb_ppdisk_masks exposes the bit-exact mask step (_create_ellipse / _substract,
+ * :188-271) alone: masks_dev is [n_comps][900][900] uint8. */
+int rsb_ppdisk_workspace_bytes(int n_images, int n_comps, size_t* bytes);
+int rsb_ppdisk_masks(const void* comps_dev, int n_comps, unsigned char* masks_dev, void* stream);
+int rsb_ppdisk_render(const void* comps_dev, int n_comps, const void* images_dev, int n_images,
+                      const float* htab_dev, int img_size, float* out_dev, void* workspace_dev,
+                      size_t workspace_bytes, void* stream);
+
 /* rsb_jet_render without any allocation, for hosts that cannot call cudaMalloc once
  * they are running: a plugin inside a process whose framework has already reserved the
  * device for its own memory pool, or a service with a device-memory budget fixed at
