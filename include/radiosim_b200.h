@@ -167,6 +167,29 @@ int rsb_ppdisk_render(const void* comps_dev, int n_comps, const void* images_dev
                       const float* htab_dev, int img_size, float* out_dev, void* workspace_dev,
                       size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------- mojave */
+/* Replaces the array work of gen_compact / gen_one_jet / gen_two_jet
+ * (src/radiosim/mojave/mojave.py:264-662): skewed-Gaussian jets (gauss.py:100-150, as pairs
+ * of host-evaluated 1-D profiles), skimage.transform.swirl (mojave.py:259), rotated Gaussians
+ * (gauss.py:50-97), skimage.transform.rotate (mojave.py:346,463,626), np.isclose zeroing and,
+ * for compact sources, the arg-max recentre and rescale (mojave.py:628-635).
+ *
+ *  recipes_dev  [n] records of 224 bytes:
+ *               {double g[3][6];            up to three [amp,x,y,sx,sy,rot] (amp 0 = unused)
+ *                double strength[2], radius[2];   swirl of jet 0 / 1, centre (size/2, size/2)
+ *                double angle;               rotation in degrees
+ *                double amp;                 compact: final amplitude
+ *                int32 blob0[2], nblob[2];   blobs of jet 0 / 1 in blobs_dev
+ *                int32 flip1;                jet 1 is added flipped in both axes (:337)
+ *                int32 compact; int32 pad[2];}
+ *  blobs_dev    records of 16 bytes {float amp; int32 pad; int64 prof;}: prof is the offset
+ *               (in floats) into profiles_dev of normal[size] followed by skew[size]
+ *  out_dev      [n][size][size] float32, or float64 with RSB_JET_OUT_F64 */
+int rsb_mojave_workspace_bytes(int n, int size, size_t* bytes);
+int rsb_mojave_render(const void* recipes_dev, int n, const void* blobs_dev,
+                      const float* profiles_dev, int size, unsigned flags, void* out_dev,
+                      void* workspace_dev, size_t workspace_bytes, void* stream);
+
 /* rsb_jet_render without any allocation, for hosts that cannot call cudaMalloc once
  * they are running: a plugin inside a process whose framework has already reserved the
  * device for its own memory pool, or a service with a device-memory budget fixed at

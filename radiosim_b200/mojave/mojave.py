@@ -1,0 +1,353 @@
+"""Drop-in ``create_mojave`` / ``gen_compact`` / ``gen_one_jet`` / ``gen_two_jet``
+(reference ``src/radiosim/mojave/mojave.py``).
+
+Host: every child generator's draws are replayed in the reference's order (scipy's
+``expon`` / ``skewnorm`` variates are drawn by calling scipy exactly as the reference does)
+and turned into a *recipe* -- skewed-Gaussian blobs as pairs of 1-D profiles, swirl
+parameters, central Gaussians, rotation angle.  Device: ``rsb_mojave_render`` evaluates the
+recipe (``radiosim_b200/csrc/mojave.cu``).  The only pixel the host ever evaluates is the one
+a shock's amplitude is read from (``mojave.py:190``), from the 1-D profiles.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+from scipy.special import ndtr
+from scipy.stats import expon, skewnorm
+
+from .. import _lib as L
+
+__all__ = ["add_swirl", "create_mojave", "gen_compact", "gen_jet", "gen_one_jet", "gen_shocks",
+           "gen_two_jet"]
+
+GAUSS = np.dtype([("amp", "<f8"), ("x", "<f8"), ("y", "<f8"), ("sx", "<f8"), ("sy", "<f8"), ("rot", "<f8")])
+RECIPE = np.dtype([("g", GAUSS, (3,)), ("strength", "<f8", (2,)), ("radius", "<f8", (2,)),
+                   ("angle", "<f8"), ("amp", "<f8"), ("blob0", "<i4", (2,)), ("nblob", "<i4", (2,)),
+                   ("flip1", "<i4"), ("compact", "<i4"), ("pad", "<i4", (2,))])
+BLOB = np.dtype([("amp", "<f4"), ("pad", "<i4"), ("prof", "<i8")])
+assert RECIPE.itemsize == 224 and BLOB.itemsize == 16
+
+
+def _as_rng(rng):
+    return np.random.default_rng(seed=rng) if isinstance(rng, (int, np.integer)) else rng
+
+
+class _Blob:
+    """amp * normal[row] * skew[col] (``src/radiosim/utils/gauss.py:131-148``)."""
+
+    __slots__ = ("amp", "normal", "skew")
+
+    def __init__(self, size, x, y, amp, width, length, a):
+        vals = np.arange(size)
+        t = (vals - y) / width
+        normal = np.exp(-(t**2) / 2.0) / np.sqrt(2 * np.pi) / width
+        self.normal = normal / normal.max()
+        u = (vals - x) / length
+        skew = 2.0 * (np.exp(-(u**2) / 2.0) / np.sqrt(2 * np.pi)) * ndtr(a * u) / length
+        self.skew = skew / skew.max()
+        self.amp = amp
+
+    def at(self, r, c):
+        v = (self.normal[r] * self.skew[c]) * self.amp
+        return 0.0 if np.isclose(v, 0) else v
+
+
+class _Jet:
+    def __init__(self, size):
+        self.size = size
+        self.blobs = []
+        self.strength = 0.0
+        self.radius = 100.0
+
+    def pixel(self, r, c):
+        """Value of the un-swirled jet image at one pixel, summed in build order."""
+        s = 0.0
+        for b in self.blobs:
+            s = s + b.at(r, c)
+        return s
+
+
+def _base_jet(size, amp, width, length, a):
+    j = _Jet(size)
+    j.blobs.append(_Blob(size, size / 2, size / 2, amp, width, length, a))
+    return j
+
+
+def _add_shocks(jet, n_shock, length, width, sx, rng):
+    """``gen_shocks`` ``:124-219``."""
+    size = jet.size
+    step = (2 * length - sx) / n_shock
+    dist = step
+    for _ in range(n_shock):
+        if rng.uniform(0, 1) > 2 / 3:
+            continue
+        px, py = size / 2 + dist, size / 2
+        r, c = int(py), int(px)
+        if not (-size <= r < size and -size <= c < size):   # the reference's IndexError
+            continue
+        s_amp = jet.pixel(r % size, c % size) * rng.uniform(0.03, 0.6)
+        s_sx = rng.uniform(*np.sort([2, width]))
+        s_sy = rng.uniform(*np.sort([s_sx, length / n_shock]))
+        s_a = rng.uniform(5, 9)
+        jet.blobs.append(_Blob(size, int(px), int(py), s_amp, s_sx, s_sy, s_a))
+        dist += step
+
+
+def _swirl(jet, rng, first=None):
+    """``add_swirl`` ``:222-261`` (draws only)."""
+    if first is None:
+        jet.strength = rng.normal(loc=0, scale=0.2)
+        jet.radius = rng.uniform(50, 200)
+    else:
+        dev = 1 + rng.normal(loc=0, scale=0.1, size=2)
+        jet.strength = first.strength * dev[0]
+        jet.radius = first.radius * dev[1]
+
+
+def _core_widths(rng, dims):
+    sx = rng.uniform(dims.min(), dims.max()) * 1.5
+    sy = rng.uniform(dims.min(), dims.max()) * 1.5
+    while sx / sy < 1 / 2 or sx / sy > 2:
+        sy = rng.uniform(dims.min(), dims.max()) * 1.5
+    return sx, sy, rng.uniform(0, 2 * np.pi)
+
+
+class _Source:
+    def __init__(self, size):
+        self.size = size
+        self.jets = []       # up to two _Jet
+        self.flip1 = False
+        self.gauss = []      # [amp, x, y, sx, sy, rot]
+        self.angle = 0.0
+        self.compact = False
+        self.amp = 0.0
+
+
+def _recipe_two_jet(rng, size):
+    """``gen_two_jet`` ``:264-398``."""
+    dev = 1 + rng.normal(loc=0, scale=0.1, size=5)
+    amp = expon.rvs(1.715e-4, 1.985e-2, random_state=rng)
+    r_w = skewnorm.rvs(4.37, 22.71, 16.85, random_state=rng) / 10
+    r_l = skewnorm.rvs(8.62, 69.60, 54.73, random_state=rng) / 4
+    r_amp = amp * rng.power(0.7)
+    l_w, l_l, l_amp = r_w * dev[2], r_l * dev[1], r_amp * dev[0]
+    dims = np.sort([r_w / 2, r_l / 5, l_w / 2, l_l / 5])
+    sx, sy, rot = _core_widths(rng, dims)
+    r_jet = _base_jet(size, r_amp, r_w, r_l, 4)
+    l_jet = _base_jet(size, l_amp, l_w, l_l, 4)
+    n_r = int(np.round(rng.power(0.5), decimals=1) * 10)
+    n_l = int(np.round(rng.power(0.5), decimals=1) * 10)
+    if n_r > 0:
+        _add_shocks(r_jet, n_r, r_l, r_w, sx, rng)
+    if n_l > 0:
+        _add_shocks(l_jet, n_l, l_l, l_w, sx, rng)
+    _swirl(r_jet, rng)
+    _swirl(l_jet, rng, r_jet)
+    s = _Source(size)
+    s.jets = [r_jet, l_jet]
+    s.flip1 = True
+    s.gauss.append([amp, size / 2, size / 2, sx, sy, rot])
+    s.angle = rng.uniform(0, 360)
+    return s
+
+
+def _recipe_one_jet(rng, size):
+    """``gen_one_jet`` ``:401-492``."""
+    amp = expon.rvs(1.715e-4, 1.985e-2, random_state=rng)
+    width = skewnorm.rvs(4.37, 22.71, 16.85, random_state=rng) / 12
+    length = skewnorm.rvs(8.62, 69.60, 54.73, random_state=rng) / 6.5
+    jet_amp = amp * rng.power(0.7)
+    dims = np.sort([width / 2, length / 5])
+    sx, sy, rot = _core_widths(rng, dims)
+    jet = _base_jet(size, jet_amp, width, length, 4)
+    n_s = int(np.round(rng.power(0.5), decimals=1) * 10)
+    if n_s > 0:
+        _add_shocks(jet, n_s, length, width, sx, rng)
+    _swirl(jet, rng)
+    s = _Source(size)
+    s.jets = [jet]
+    s.gauss.append([amp, size / 2, size / 2, sx, sy, rot])
+    s.angle = rng.uniform(0, 360)
+    return s
+
+
+def _bounded_width(rng, dims):
+    v = rng.uniform(*dims) * 1.7
+    tries = 0
+    while v > 15:
+        if tries > 10:
+            v /= 5
+            break
+        v = rng.uniform(*dims) * 1.7
+        tries += 1
+    return v
+
+
+def _recipe_compact(rng, size):
+    """``gen_compact`` ``:495-662``."""
+    ncomps = rng.integers(1, 4)
+    outflow = rng.uniform() > 0.5
+    amp = expon.rvs(5.54e-05, 0.02, random_state=rng)
+    jet_amp = amp * rng.normal(2 / 3, 0.05)
+    width = skewnorm.rvs(8.41, 3.04, 3.46, random_state=rng) * 0.8
+    length = skewnorm.rvs(6.04, 3.02, 2.59, random_state=rng) * 1
+    s = _Source(size)
+    if outflow:
+        jet = _base_jet(size, jet_amp, width, length, 4)
+        _swirl(jet, rng)
+        s.jets = [jet]
+    dims = np.sort([width / 2, length / 4])
+    dims[0] *= 1.2
+    dims = np.sort(dims)
+    c_sx, c_sy, c_rot = [], [], []
+    vertical = True
+    for i in range(int(ncomps)):
+        dev = 1 + rng.normal(loc=0, scale=0.2, size=2)
+        if i != 0:
+            ox, oy = rng.uniform(-5, 5), rng.uniform(-5, 5)
+        else:
+            ox = oy = 0
+        if i == 0:
+            sx = _bounded_width(rng, dims)
+            sy = _bounded_width(rng, dims)
+            tries = 0
+            while (sx / sy < 0.33 or sx / sy > 3) or (0.75 < sx / sy < 1.33):
+                if tries > 10:
+                    sy = sx * rng.choice([rng.uniform(0.4, 0.8), rng.uniform(1.2, 2.5)])
+                    if sy > 15:
+                        sy /= 5
+                    break
+                sy = _bounded_width(rng, dims)
+                tries += 1
+            vertical = sx > sy
+        else:
+            sx, sy = c_sx[-1] * dev[0], c_sy[-1] * dev[1]
+        if c_rot:
+            rot = rng.uniform(c_rot[-1] - 0.1, c_rot[-1] + 0.1)
+        elif vertical:
+            rot = rng.uniform(-np.pi / 4, np.pi / 4)
+        else:
+            rot = rng.uniform(-np.pi / 4 + np.pi / 2, np.pi / 4 + np.pi / 2)
+        c_amp = amp * rng.uniform(0.5, 1.2)
+        s.gauss.append([c_amp, size / 2 - ox, size / 2 - oy, sx, sy, rot])
+        c_sx.append(sx)
+        c_sy.append(sy)
+        c_rot.append(rot)
+    s.angle = rng.uniform(0, 360)
+    s.compact = True
+    s.amp = amp
+    return s
+
+
+def render_sources(sources, size, f64=True, chunk=2048):
+    """Evaluate recipes on the device -> ``[n, size, size]`` float64 (or float32)."""
+    L.require_device()
+    lib = L.lib()
+    n = len(sources)
+    dt = np.float64 if f64 else np.float32
+    out = np.empty((n, size, size), dtype=dt)
+    max_imgs = max(1, min(chunk, (1 << 30) // (size * size * 8)))
+    for i0 in range(0, n, max_imgs):
+        part = sources[i0 : i0 + max_imgs]
+        rec = np.zeros(len(part), dtype=RECIPE)
+        blobs, profs = [], []
+        for k, s in enumerate(part):
+            r = rec[k]
+            for q, g in enumerate(s.gauss):
+                r["g"][q] = tuple(g)
+            for q, j in enumerate(s.jets):
+                r["blob0"][q] = len(blobs)
+                r["nblob"][q] = len(j.blobs)
+                r["strength"][q], r["radius"][q] = j.strength, j.radius
+                for b in j.blobs:
+                    blobs.append((np.float32(b.amp), 0, 2 * size * len(profs)))
+                    profs.append(np.concatenate((b.normal, b.skew)).astype(np.float32))
+            r["angle"], r["amp"] = s.angle, s.amp
+            r["flip1"], r["compact"] = int(s.flip1), int(s.compact)
+        blob_arr = np.array(blobs, dtype=BLOB) if blobs else np.zeros(1, dtype=BLOB)
+        prof_arr = np.concatenate(profs) if profs else np.zeros(2 * size, dtype=np.float32)
+        need = C.c_size_t(0)
+        L.check(lib.rsb_mojave_workspace_bytes(len(part), size, C.byref(need)))
+        d_r, d_b, d_p = L.dev_from(rec), L.dev_from(blob_arr), L.dev_from(prof_arr)
+        d_w = L.DeviceBuffer(need.value)
+        d_o = L.DeviceBuffer(len(part) * size * size * np.dtype(dt).itemsize)
+        L.check(lib.rsb_mojave_render(d_r.ptr, len(part), d_b.ptr, d_p.ptr, size,
+                                      L.JET_OUT_F64 if f64 else 0, d_o.ptr, d_w.ptr, d_w.nbytes, None),
+                "rsb_mojave_render")
+        out[i0 : i0 + len(part)] = d_o.download((len(part), size, size), dt)
+    return out
+
+
+def gen_two_jet(rng, size=1024, printout=False):
+    return render_sources([_recipe_two_jet(_as_rng(rng), size)], size)[0]
+
+
+def gen_one_jet(rng, size=1024, printout=False):
+    return render_sources([_recipe_one_jet(_as_rng(rng), size)], size)[0]
+
+
+def gen_compact(rng, size=1024, printout=False):
+    return render_sources([_recipe_compact(_as_rng(rng), size)], size)[0]
+
+
+def gen_jet(size, amplitude, width, length, a):
+    """``gen_jet`` ``:84-121`` as an image (device render of a single un-swirled blob)."""
+    s = _Source(size)
+    j = _base_jet(size, amplitude, width, length, a)
+    j.strength, j.radius = 0.0, 100.0
+    s.jets = [j]
+    return render_sources([s], size)[0]
+
+
+def gen_shocks(*args, **kwargs):  # pragma: no cover - kept for API completeness
+    raise NotImplementedError("gen_shocks operates on host images in the reference; here shocks "
+                              "are part of the recipe (see _add_shocks)")
+
+
+def add_swirl(*args, **kwargs):  # pragma: no cover
+    raise NotImplementedError("add_swirl is fused into rsb_mojave_render; see _swirl")
+
+
+def class_counts(class_ratio, bundle_size):
+    """``create_mojave`` ``:47-53``."""
+    ratio = np.array(class_ratio)
+    amount = np.array((ratio / ratio.sum()) * bundle_size).astype(int)
+    while amount.sum() < bundle_size:
+        amount[amount.argmax()] += 1
+    return amount
+
+
+def create_mojave(conf, rng, today=None):
+    """Drop-in for ``create_mojave`` (``:23-81``): ``(data, data_name)``.
+
+    ``general.threads`` is validated like the reference (``:38-42``) but unused: the child
+    generators are consumed in order on the host and rendered in one device batch.
+    """
+    threads = conf.general.threads
+    if not threads:
+        threads = 1
+    elif not isinstance(threads, int) or threads <= 0:
+        raise ValueError("threads has to be int > 0 or None")
+    size = conf.dataset.img_size
+    bundle_size = conf.dataset.bundle_size
+    amount = class_counts(conf.mojave.class_ratio, bundle_size)
+    sources = [_recipe_compact(c, size) for c in rng.spawn(amount[0])]
+    sources += [_recipe_one_jet(c, size) for c in rng.spawn(amount[1])]
+    sources += [_recipe_two_jet(c, size) for c in rng.spawn(amount[2])]
+    jets = render_sources(sources, size)
+    classes = np.repeat(np.arange(3), amount)
+    order = np.arange(bundle_size)
+    rng.shuffle(order)
+    ra = rng.uniform(0, 360, size=bundle_size)      # utils.py:386-390
+    dec = rng.uniform(-30, 87, size=bundle_size)
+    start = np.datetime64("1995-01-01")             # utils.py:393-406
+    if today is None:
+        from datetime import datetime
+
+        today = datetime.now().date()
+    delta = np.datetime64(today) - start
+    dates = start + rng.integers(delta.astype(int), size=bundle_size)
+    data = [jets[order], classes[order], ra[order], dec[order], dates.astype("S10")]
+    return data, ["galaxies", "galaxy_classes", "RA", "DEC", "date"]
