@@ -190,6 +190,19 @@ int rsb_mojave_render(const void* recipes_dev, int n, const void* blobs_dev,
                       const float* profiles_dev, int size, unsigned flags, void* out_dev,
                       void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------- utilities */
+/* idx of zoom_on_source (src/radiosim/utils/utils.py:111-119): smallest distance from any
+ * pixel > threshold to the border of a size x size float64 image; `size` if there is none
+ * (the reference then uses idx = 0).  margin_dev: one int32. */
+int rsb_source_margin(const double* img_dev, int size, double threshold, int* margin_dev,
+                      void* stream);
+/* cv2.resize(np.pad(src, pad), (dst_size, dst_size), INTER_LINEAR) on float64
+ * (zoom_on_source utils.py:124-135 with pad = 0 on a crop, zoom_out utils.py:161-166).
+ * `planes` images: plane p starts at src_dev + p * src_plane_stride, rows `src_pitch` apart;
+ * dst_dev is [planes][dst_size][dst_size]. */
+int rsb_resize_linear(const double* src_dev, int src_size, int src_pitch, size_t src_plane_stride,
+                      int pad, int planes, double* dst_dev, int dst_size, void* stream);
+
 /* rsb_jet_render without any allocation, for hosts that cannot call cudaMalloc once
  * they are running: a plugin inside a process whose framework has already reserved the
  * device for its own memory pool, or a service with a device-memory budget fixed at

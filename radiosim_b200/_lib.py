@@ -68,6 +68,8 @@ _SIGS = {
     "rsb_ppdisk_render": ([_vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _sz, _vp], _i32),
     "rsb_mojave_workspace_bytes": ([_i32, _i32, C.POINTER(_sz)], _i32),
     "rsb_mojave_render": ([_vp, _i32, _vp, _vp, _i32, _u32, _vp, _vp, _sz, _vp], _i32),
+    "rsb_source_margin": ([_vp, _i32, C.c_double, _vp, _vp], _i32),
+    "rsb_resize_linear": ([_vp, _i32, _i32, _sz, _i32, _i32, _vp, _i32, _vp], _i32),
     "rsb_jet_render_host": ([_vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp], _i32),
 }
 for _name, (_args, _res) in _SIGS.items():
