@@ -67,6 +67,7 @@ struct __align__(16) Fixed2 {
   float delta[2];
   int dlo[2];                       // no pixel closer than this to the border exceeds 0.01
   struct LabelReq { unsigned long long best; int img, pb, margin, zpad; } label[2];  // [image parity]
+  float geo[kMaxSlots * 8];         // build_coefs2 scratch (SlotGeo per live slot)
   int ncand;                        // borderline pixels awaiting a float64 verdict
   int cand[kMaxCand];               // r << 16 | c
   unsigned char tile_order[kMaxTiles];  // tiles sorted by distance from the image centre
@@ -117,94 +118,125 @@ __device__ __forceinline__ void store_out4(char* out_row, bool f64, int c0, int 
   }
 }
 
-// ---- warp 0: parameter block -> compacted coefficients + culling spans ------------
-// Ellipse of the > tau footprint: z^T M z <= T^2 with z = (dr, dc).  For a row range
+// ---- one warp: parameter block -> compacted coefficients + culling spans + dlo ---------
+// Runs while the other warps render the previous image, so it is written for latency:
+// float32 throughout (only the centre split needs the float64 parameters) and every lane
+// busy.  Ellipse of the > tau footprint: z^T M z <= T^2 with z = (dr, dc).  For a row range
 // the covered columns are [min cl, max cr], cl/cr = centre line -/+ half width; cr is
 // concave in dr, so its maximum over the range is the ellipse's rightmost point if that
 // row lies in the range, else the larger end value (mirror image for cl).
+struct SlotGeo {  // per live slot, shared between the lanes through shared memory
+  float Mrr, Mcc, Mrc, T2, ec, x, y;
+  int degenerate;
+};
+
 __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
                                     int H, int lane, bool zoom) {
+  SlotGeo* geo = reinterpret_cast<SlotGeo*>(sm.geo);
   float amax = 0.f;
   for (int k = lane; k < slots; k += 32) amax = fmaxf(amax, fabsf((float)P[k * 6]));
   amax = warp_max(amax);
-  const double tau = 2e-8 * (double)amax;  // <= 19 x 2e-8 of the peak is dropped in total
+  const float tau = 2e-8f * amax;  // <= 19 x 2e-8 of the peak is dropped in total
   const int ngroups = (H + kTileRows - 1) / kTileRows;
   int base = 0;
-  for (int k0 = 0; k0 < slots; k0 += 32) {
+  // frame bound (dlo) inputs of this lane's slots: k = lane, lane + 32
+  float ka[2] = {0.f, 0.f}, kx[2] = {0.f, 0.f}, ky[2] = {0.f, 0.f}, cx[2] = {0.f, 0.f}, cy[2] = {0.f, 0.f};
+  bool certified = false, all_nonneg = true;
+  for (int k0 = 0, h = 0; k0 < slots; k0 += 32, ++h) {
     const int k = k0 + lane;
     bool live = false;
     Coef c;
-    double Mrr = 0, Mcc = 0, Mrc = 0, T2 = 0, ec = 0, x = 0, y = 0;
-    bool degenerate = false;
+    SlotGeo g;
+    g.degenerate = 0;
     if (k < slots) {
       const double* p = P + k * 6;
-      const double amp = p[0], sx = p[3], sy = p[4];
-      x = p[1];
-      y = p[2];
-      if (amp != 0.0 && fabs(amp) > tau) {
-        double sr, cr;
-        sincos(p[5], &sr, &cr);
-        const double iu = 1.0 / (sy * sy), iv = 1.0 / (sx * sx);
-        Mrr = cr * cr * iu + sr * sr * iv;
-        Mcc = sr * sr * iu + cr * cr * iv;
-        Mrc = sr * cr * (iv - iu);
-        const double h = 0.5 * 1.4426950408889634;  // exponent = -(z^T M z)/2 * log2(e)
-        c.A = (float)(-h * Mcc);
-        c.C = (float)(-h * Mrr);
-        c.B = (float)(-2.0 * h * Mrc);
-        c.amp = (float)amp;
-        const double yr = rint(y), xr = rint(x);
+      const double xd = p[1], yd = p[2];
+      const float amp = (float)p[0], sx = (float)p[3], sy = (float)p[4];
+      if (p[0] != 0.0 && fabsf(amp) > tau) {
+        float sr, cr;
+        sincosf((float)p[5], &sr, &cr);
+        const float iu = 1.f / (sy * sy), iv = 1.f / (sx * sx);
+        g.Mrr = cr * cr * iu + sr * sr * iv;
+        g.Mcc = sr * sr * iu + cr * cr * iv;
+        g.Mrc = sr * cr * (iv - iu);
+        const float hl = 0.72134752f;  // log2(e) / 2
+        c.A = -hl * g.Mcc;
+        c.C = -hl * g.Mrr;
+        c.B = -2.f * hl * g.Mrc;
+        c.amp = amp;
+        const double yr = rint(yd), xr = rint(xd);
         c.irf = (float)yr;
-        c.fr = (float)(y - yr);
+        c.fr = (float)(yd - yr);
         c.icf = (float)xr;
-        c.fc = (float)(x - xr);
-        T2 = 2.0 * log(fabs(amp) / tau);
-        const double det = Mrr * Mcc - Mrc * Mrc;
-        const double er = sqrt(T2 * Mcc / det);
-        ec = sqrt(T2 * Mrr / det);
-        degenerate = !(isfinite(er) && isfinite(ec));
-        const double lo_r = fmax(floor(y - er) - 1.0, 0.0), hi_r = fmin(ceil(y + er) + 1.0, N - 1.0);
-        const double lo_c = fmax(floor(x - ec) - 1.0, 0.0), hi_c = fmin(ceil(x + ec) + 1.0, N - 1.0);
-        if (degenerate) {
+        c.fc = (float)(xd - xr);
+        g.x = (float)xd;
+        g.y = (float)yd;
+        g.T2 = 2.f * logf(fabsf(amp) / tau);
+        const float det = g.Mrr * g.Mcc - g.Mrc * g.Mrc;
+        const float er = sqrtf(g.T2 * g.Mcc / det);
+        g.ec = sqrtf(g.T2 * g.Mrr / det);
+        g.degenerate = !(isfinite(er) && isfinite(g.ec));
+        const float lo_r = fmaxf(floorf(g.y - er) - 1.f, 0.f), hi_r = fminf(ceilf(g.y + er) + 1.f, N - 1.f);
+        const float lo_c = fmaxf(floorf(g.x - g.ec) - 1.f, 0.f), hi_c = fminf(ceilf(g.x + g.ec) + 1.f, N - 1.f);
+        if (g.degenerate) {
           live = true;
           c.r0 = 0; c.r1 = N - 1; c.c0 = 0; c.c1 = N - 1;
         } else if (lo_r <= hi_r && lo_c <= hi_c) {
           live = true;
           c.r0 = (int)lo_r; c.r1 = (int)hi_r; c.c0 = (int)lo_c; c.c1 = (int)hi_c;
         }
+        if (h < 2) {
+          ka[h] = fabsf(amp) * 1.0001f;
+          kx[h] = (det / g.Mrr) * 0.9999f * hl;
+          ky[h] = (det / g.Mcc) * 0.9999f * hl;
+          cx[h] = g.x;
+          cy[h] = g.y;
+          // the pixel nearest to the centre is at most half a pixel away in each coordinate:
+          // this slot alone lifts it above the threshold -> the > 0.01 mask is not empty
+          const float qmax = 0.25f * (g.Mrr + g.Mcc + 2.f * fabsf(g.Mrc));
+          if (amp * __expf(-0.5f * qmax) > 0.0101f && g.x >= 0.f && g.x <= N - 1.f && g.y >= 0.f &&
+              g.y <= N - 1.f)
+            certified = true;
+        }
       }
+      if (p[0] < 0.0) all_nonneg = false;
+      if (p[0] != 0.0 && h >= 2) all_nonneg = false;  // > 64 slots: no frame bound
     }
     const unsigned mask = __ballot_sync(0xffffffffu, live);
     if (live) {
       const int pos = base + __popc(mask & ((1u << lane) - 1u));
       sm.coef[cb][pos] = c;
-      // float32 is plenty here: the interval is widened by one pixel on each side
-      const float fMrr = (float)Mrr, fMcc = (float)Mcc, fMrc = (float)Mrc, fT2 = (float)T2;
-      const float fdet = fMrr * fMcc - fMrc * fMrc, fec = (float)ec, fx = (float)x, fy = (float)y;
-      const float dr_right = -fMrc * fec / fMrr;  // row offset of the rightmost point
-      const float inv_cc = 1.f / fMcc, slope = -fMrc * inv_cc;
-      for (int g = 0; g < ngroups; ++g) {
-        const int ga = max(R0 + g * kTileRows, c.r0);
-        const int gb = min(min(R0 + g * kTileRows + kTileRows - 1, R0 + H - 1), c.r1);
-        int packed = 0x7fff;  // lo = 32767 > hi = 0: empty
-        if (ga <= gb) {
-          int lo_i = c.c0, hi_i = c.c1;
-          if (!degenerate) {
-            const float da = (float)ga - fy, db = (float)gb - fy;
-            const float hwa = sqrtf(fmaxf(fT2 * fMcc - fdet * da * da, 0.f)) * inv_cc;
-            const float hwb = sqrtf(fmaxf(fT2 * fMcc - fdet * db * db, 0.f)) * inv_cc;
-            const float cla = slope * da, clb = slope * db;
-            const float hi = (da <= dr_right && dr_right <= db) ? fec : fmaxf(cla + hwa, clb + hwb);
-            const float lo = (da <= -dr_right && -dr_right <= db) ? -fec : fminf(cla - hwa, clb - hwb);
-            lo_i = max((int)floorf(fx + lo) - 1, c.c0);
-            hi_i = min((int)ceilf(fx + hi) + 1, c.c1);
-          }
-          if (lo_i <= hi_i) packed = lo_i | (hi_i << 16);
-        }
-        sm.span[cb][pos][g] = packed;
-      }
+      geo[pos] = g;
     }
     base += __popc(mask);
+  }
+  __syncwarp();
+  // culling spans: (slot, row group) pairs dealt over the lanes
+  for (int e = lane; e < base * ngroups; e += 32) {
+    const int pos = e / ngroups, gi = e - pos * ngroups;
+    const SlotGeo g = geo[pos];
+    const Coef& c = sm.coef[cb][pos];
+    const int ga = max(R0 + gi * kTileRows, c.r0);
+    const int gb = min(min(R0 + gi * kTileRows + kTileRows - 1, R0 + H - 1), c.r1);
+    int packed = 0x7fff;  // lo = 32767 > hi = 0: empty
+    if (ga <= gb) {
+      int lo_i = c.c0, hi_i = c.c1;
+      if (!g.degenerate) {
+        const float det = g.Mrr * g.Mcc - g.Mrc * g.Mrc;
+        const float dr_right = -g.Mrc * g.ec / g.Mrr;  // row offset of the rightmost point
+        const float inv_cc = 1.f / g.Mcc, slope = -g.Mrc * inv_cc;
+        const float da = (float)ga - g.y, db = (float)gb - g.y;
+        const float hwa = sqrtf(fmaxf(g.T2 * g.Mcc - det * da * da, 0.f)) * inv_cc;
+        const float hwb = sqrtf(fmaxf(g.T2 * g.Mcc - det * db * db, 0.f)) * inv_cc;
+        const float cla = slope * da, clb = slope * db;
+        const float hi = (da <= dr_right && dr_right <= db) ? g.ec : fmaxf(cla + hwa, clb + hwb);
+        const float lo = (da <= -dr_right && -dr_right <= db) ? -g.ec : fminf(cla - hwa, clb - hwb);
+        lo_i = max((int)floorf(g.x + lo) - 1, c.c0);
+        hi_i = min((int)ceilf(g.x + hi) + 1, c.c1);
+      }
+      if (lo_i <= hi_i) packed = lo_i | (hi_i << 16);
+    }
+    sm.span[cb][pos][gi] = packed;
   }
   // Zoom images only use the crop [margin, N-margin)^2 of the raw image, and margin >= dlo,
   // where dlo is the smallest border distance d at which an UPPER BOUND of the image over
@@ -213,37 +245,7 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
   // amp * exp(-q/2) with q the smallest Mahalanobis distance to the four frame lines.
   int dlo = 0;
   if (zoom) {
-    // per-slot constants (slots k = lane and lane + 32), float32 with a safety margin
-    float ka[2], kx[2], ky[2], cx[2], cy[2];
-    bool certified = false, all_nonneg = true;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int k = lane + 32 * h;
-      ka[h] = 0.f; kx[h] = ky[h] = 0.f; cx[h] = cy[h] = 0.f;
-      if (k < slots && P[k * 6] != 0.0) {
-        const double* p = P + k * 6;
-        double sr, cr;
-        sincos(p[5], &sr, &cr);
-        const double iu = 1.0 / (p[4] * p[4]), iv = 1.0 / (p[3] * p[3]);
-        const double mrr = cr * cr * iu + sr * sr * iv, mcc = sr * sr * iu + cr * cr * iv;
-        const double mrc = sr * cr * (iv - iu);
-        const double det = mrr * mcc - mrc * mrc;
-        ka[h] = (float)fabs(p[0]) * 1.0001f;
-        kx[h] = (float)(det / mrr) * 0.9999f * 0.72134752f;  // * log2(e)/2
-        ky[h] = (float)(det / mcc) * 0.9999f * 0.72134752f;
-        cx[h] = (float)p[1];
-        cy[h] = (float)p[2];
-        if (p[0] < 0.0) all_nonneg = false;
-        // the pixel nearest to the centre is at most half a pixel away in each coordinate:
-        // this slot alone lifts it above the threshold -> the > 0.01 mask is not empty
-        const double qmax = 0.25 * (mrr + mcc + 2.0 * fabs(mrc));
-        if (p[0] * exp(-0.5 * qmax) > 0.0101 && p[1] >= 0.0 && p[1] <= N - 1.0 && p[2] >= 0.0 &&
-            p[2] <= N - 1.0)
-          certified = true;
-      }
-    }
-    certified = __any_sync(0xffffffffu, certified) && __all_sync(0xffffffffu, all_nonneg) &&
-                slots <= 64;
+    certified = __any_sync(0xffffffffu, certified) && __all_sync(0xffffffffu, all_nonneg);
     auto frame_bound = [&](int d) -> float {
       const float lo = (float)d, hi = (float)(N - 1 - d);
       float u = 0.f;
