@@ -391,6 +391,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   int* tab_i = reinterpret_cast<int*>(tab_w + 3 * npad);               // [npad] first tap (absolute)
   float* raw = reinterpret_cast<float*>(tab_i + npad);                 // [H (+1 halo)][pitch]
 
+  const uint32_t s_raw = smem_u32(raw), s_tabw = smem_u32(tab_w), s_tabi = smem_u32(tab_i);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rank = (kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0;
   const int cid = blockIdx.x / kCluster, nclusters = gridDim.x / kCluster;
@@ -530,8 +531,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const int nlive = sm.nlive[buf];
     const float thr = (float)kEdgeThr, delta = sm.delta[buf];
     const int dlo = sm.dlo[buf];
-    const Coef* coef = sm.coef[buf];
-    const int (*span)[kMaxGroups] = sm.span[buf];
+    const uint32_t s_coef = smem_u32(sm.coef[buf]), s_span = smem_u32(sm.span[buf]);
 
     // ---------------- phase 1: splat this CTA's band, 8 x 64 tiles ------------------
     int my_margin = N;
@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       const int ta = sm.tile_order[t];  // central (heavy) tiles first, light corners last
       const int g = __float2int_rz(((float)ta + 0.5f) * inv_tcols), tc = ta - g * tcols;
       const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
-      float* dst = raw + (size_t)(r0 - base) * pitch;
+      const uint32_t s_dst = s_raw + (uint32_t)((r0 - base) * pitch + c0) * 4u;
       const int rend = min(R0 + H, r0 + kTileRows);  // rows of this tile that exist
       {
         // every pixel of the tile closer than dlo to the border: never read, never above 0.01
@@ -563,15 +563,15 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       for (int k0 = 0; k0 < nlive; k0 += 32) {
         bool hit = false;
         if (k0 + lane < nlive) {
-          const int sp = span[k0 + lane][g];
+          const int sp = lds_s32(s_span + (uint32_t)((k0 + lane) * kMaxGroups + g) * 4u);
           hit = !((sp >> 16) < tc0 || (sp & 0xffff) > tc0 + kTileCols - 1);
         }
         unsigned hits = __ballot_sync(0xffffffffu, hit);
         while (hits) {
           const int k = k0 + __ffs(hits) - 1;
           hits &= hits - 1;
-          const float4 q = *reinterpret_cast<const float4*>(&coef[k].A);     // A B C amp
-          const float4 ct = *reinterpret_cast<const float4*>(&coef[k].irf);  // irf fr icf fc
+          const float4 q = lds_v4(s_coef + (uint32_t)k * 48u);        // A B C amp
+          const float4 ct = lds_v4(s_coef + (uint32_t)k * 48u + 16u);  // irf fr icf fc
           const float d0 = (c0f - ct.z) - ct.w;
           const f2 d = f2_pack(d0, d0 + 1.f);
           const f2 Q = f2_mul(f2_pack(q.y, q.y), d);
@@ -602,7 +602,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
         for (int i = 0; i < kTileRows; ++i) {
           if (r0 + i < rend) {
-            *reinterpret_cast<float2*>(dst + (size_t)i * pitch + c0) = make_float2(acc[i][0], acc[i][1]);
+            sts_v2(s_dst + (uint32_t)(i * pitch) * 4u, acc[i][0], acc[i][1]);
             tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
           }
         }
@@ -676,7 +676,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       for (int e = tid; e < H * q4; e += kWorkers) {
         const int rl = e / q4, c0 = (e - rl * q4) << 2;
         const int r = R0 + rl;
-        float4 v = *reinterpret_cast<const float4*>(raw + (size_t)(r - base) * pitch + c0);
+        float4 v = lds_v4(s_raw + (uint32_t)((r - base) * pitch + c0) * 4u);
         v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
         if (bulk) *reinterpret_cast<float4*>(raw + (size_t)(r - base) * pitch + c0) = v;
         else store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
@@ -775,16 +775,16 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         // rows are dealt statically; inactive strips carry zero weights and index 0, so the
         // gathers need no branches (24 independent loads in flight per row)
         for (int r = rlo + warp; r < rhi; r += kWarps) {
-          float* row = raw + (size_t)(r - base) * pitch;
+          const uint32_t s_row = s_raw + (uint32_t)((r - base) * pitch) * 4u;
           float v[NS][4][3];
 #pragma unroll
           for (int s = 0; s < NS; ++s)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const float* src = row + ct[s][j].i;
-              v[s][j][0] = src[0];
-              v[s][j][1] = src[1];
-              v[s][j][2] = src[2];
+              const uint32_t src = s_row + (uint32_t)ct[s][j].i * 4u;
+              v[s][j][0] = lds_f32(src);
+              v[s][j][1] = lds_f32(src + 4u);
+              v[s][j][2] = lds_f32(src + 8u);
             }
           float res[NS][4];
 #pragma unroll
@@ -801,7 +801,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int cj = s * kStrip + 32 * j + lane;
-                if (cj < N) row[cj] = res[s][j];
+                if (cj < N) sts_f32(s_row + (uint32_t)cj * 4u, res[s][j]);
               }
             }
           }
@@ -837,19 +837,20 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
         for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < vr0 || r > vr1) continue;  // warp-uniform
-        const float w0 = tab_w[r], w1 = tab_w[npad + r], w2 = tab_w[2 * npad + r];
+        const float w0 = lds_f32(s_tabw + (uint32_t)r * 4u), w1 = lds_f32(s_tabw + (uint32_t)(npad + r) * 4u),
+                    w2 = lds_f32(s_tabw + (uint32_t)(2 * npad + r) * 4u);
         // only zero-weight taps can fall outside this band (+ halo): clamp them
-        const int l0 = tab_i[r] - base;
-        const float* p0 = raw + (size_t)min(max(l0, 0), H) * pitch;
-        const float* p1 = raw + (size_t)min(max(l0 + 1, 0), H) * pitch;
-        const float* p2 = raw + (size_t)min(max(l0 + 2, 0), H) * pitch;
+        const int l0 = lds_s32(s_tabi + (uint32_t)r * 4u) - base;
+        const uint32_t p0 = s_raw + (uint32_t)(min(max(l0, 0), H) * pitch) * 4u;
+        const uint32_t p1 = s_raw + (uint32_t)(min(max(l0 + 1, 0), H) * pitch) * 4u;
+        const uint32_t p2 = s_raw + (uint32_t)(min(max(l0 + 2, 0), H) * pitch) * 4u;
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
           const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
           if (!(s < strips && sc0 <= fhi && sc0 + kStrip - 1 >= flo) || c0 >= N) continue;
-          const float4 t0 = *reinterpret_cast<const float4*>(p0 + c0);
-          const float4 t1 = *reinterpret_cast<const float4*>(p1 + c0);
-          const float4 t2 = *reinterpret_cast<const float4*>(p2 + c0);
+          const float4 t0 = lds_v4(p0 + (uint32_t)c0 * 4u);
+          const float4 t1 = lds_v4(p1 + (uint32_t)c0 * 4u);
+          const float4 t2 = lds_v4(p2 + (uint32_t)c0 * 4u);
           float4 v;
           {
             const f2 W0 = f2_pack(w0, w0), W1 = f2_pack(w1, w1), W2 = f2_pack(w2, w2);
