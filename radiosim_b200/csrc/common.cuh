@@ -83,6 +83,18 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 // window base depends on the CTA's rank in the cluster; with generic pointers the compiler
 // kept re-deriving it (S2R SR_CgaCtaId + address arithmetic) in front of loads and stores in
 // the hot loops.  An address computed once and passed to ld/st.shared avoids that.
+// Launder a value through an empty asm so that ptxas keeps it in a register instead of
+// re-deriving it (it happily re-reads SR_TID / SR_CgaCtaId -- ~100 cycles each -- in front of
+// every guarded store).
+__device__ __forceinline__ uint32_t keep_u32(uint32_t v) {
+  asm volatile("mov.u32 %0, %0;" : "+r"(v));
+  return v;
+}
+__device__ __forceinline__ int keep_s32(int v) {
+  asm volatile("mov.s32 %0, %0;" : "+r"(v));
+  return v;
+}
+
 __device__ __forceinline__ float lds_f32(uint32_t a) {
   float v;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));

@@ -391,8 +391,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   int* tab_i = reinterpret_cast<int*>(tab_w + 3 * npad);               // [npad] first tap (absolute)
   float* raw = reinterpret_cast<float*>(tab_i + npad);                 // [H (+1 halo)][pitch]
 
-  const uint32_t s_raw = smem_u32(raw), s_tabw = smem_u32(tab_w), s_tabi = smem_u32(tab_i);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t s_raw = keep_u32(smem_u32(raw)), s_tabw = keep_u32(smem_u32(tab_w)),
+                 s_tabi = keep_u32(smem_u32(tab_i));
+  const int tid = keep_s32((int)threadIdx.x), lane = tid & 31, warp = tid >> 5;
   const int rank = (kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0;
   const int cid = blockIdx.x / kCluster, nclusters = gridDim.x / kCluster;
   const int H = N / kCluster;                // rows of this CTA's band (N even when kCluster == 2)
@@ -531,7 +532,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const int nlive = sm.nlive[buf];
     const float thr = (float)kEdgeThr, delta = sm.delta[buf];
     const int dlo = sm.dlo[buf];
-    const uint32_t s_coef = smem_u32(sm.coef[buf]), s_span = smem_u32(sm.span[buf]);
+    const uint32_t s_coef = keep_u32(smem_u32(sm.coef[buf])), s_span = keep_u32(smem_u32(sm.span[buf]));
 
     // ---------------- phase 1: splat this CTA's band, 8 x 64 tiles ------------------
     int my_margin = N;
@@ -782,9 +783,13 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               const uint32_t src = s_row + (uint32_t)ct[s][j].i * 4u;
+#ifdef RSB_DBG_NOGATHER
+              v[s][j][0] = v[s][j][1] = v[s][j][2] = __uint_as_float(src);
+#else
               v[s][j][0] = lds_f32(src);
               v[s][j][1] = lds_f32(src + 4u);
               v[s][j][2] = lds_f32(src + 8u);
+#endif
             }
           float res[NS][4];
 #pragma unroll
@@ -798,10 +803,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
           for (int s = 0; s < NS; ++s) {
             if (act[s]) {
+              const uint32_t s_out = s_row + (uint32_t)(s * kStrip + lane) * 4u;
+              if ((s + 1) * kStrip <= N) {  // whole strip inside the image (warp-uniform)
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const int cj = s * kStrip + 32 * j + lane;
-                if (cj < N) sts_f32(s_row + (uint32_t)cj * 4u, res[s][j]);
+                for (int j = 0; j < 4; ++j) sts_f32(s_out + 128u * j, res[s][j]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (s * kStrip + 32 * j + lane < N) sts_f32(s_out + 128u * j, res[s][j]);
               }
             }
           }
