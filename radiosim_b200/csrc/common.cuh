@@ -90,6 +90,10 @@ __device__ __forceinline__ uint32_t keep_u32(uint32_t v) {
   asm volatile("mov.u32 %0, %0;" : "+r"(v));
   return v;
 }
+__device__ __forceinline__ float keep_f32(float v) {
+  asm volatile("mov.f32 %0, %0;" : "+f"(v));
+  return v;
+}
 __device__ __forceinline__ int keep_s32(int v) {
   asm volatile("mov.s32 %0, %0;" : "+r"(v));
   return v;
@@ -105,9 +109,34 @@ __device__ __forceinline__ int lds_s32(uint32_t a) {
   asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
   return v;
 }
+__device__ __forceinline__ int lds_u16(uint32_t a) {
+  unsigned short v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+  return (int)v;
+}
+__device__ __forceinline__ int atoms_add(uint32_t a, int v) {
+  int r;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(a), "r"(v) : "memory");
+  return r;
+}
 __device__ __forceinline__ float4 lds_v4(uint32_t a) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float2 lds_v2(uint32_t a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint2 lds_v2u(uint32_t a) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint4 lds_v4u(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
   return v;
 }
 __device__ __forceinline__ void sts_f32(uint32_t a, float v) {

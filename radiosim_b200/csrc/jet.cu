@@ -515,7 +515,7 @@ int rsb_jet_workspace_bytes(int n, int slots, int size, size_t* bytes) {
   {
     int cluster = 1;
     size_t smem = 0;
-    if (v2_supported(size, &cluster, &smem)) {
+    if (v2_supported(size, slots, &cluster, &smem)) {
       *bytes = 0;
       return 0;
     }
@@ -541,7 +541,7 @@ int rsb_jet_render(const double* params, const int32_t* zoom_pad, int n, int slo
   {
     int cluster = 1;
     size_t smem = 0;
-    if (v2_supported(size, &cluster, &smem)) {  // on-chip path: no scratch at all
+    if (v2_supported(size, slots, &cluster, &smem)) {  // on-chip path: no scratch at all
       Args a2;
       a2.params = params; a2.zoom_pad = zoom_pad; a2.n = n; a2.slots = slots; a2.size = size;
       a2.flags = flags; a2.out = out_img; a2.margin = out_margin; a2.peak = out_peak;

@@ -32,11 +32,16 @@ namespace v2 {
 
 #ifdef RSB_TIMELINE
 __device__ long long* g_timeline = nullptr;  // [image][rank][16] clock64 stamps (debug builds)
-#define RSB_STAMP_T(k, t) do { if (g_timeline && tid == (t)) g_timeline[((size_t)img * 2 + rank) * 16 + (k)] = clock64(); } while (0)
-#define RSB_STAMP(k) do { if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 16 + (k)] = clock64(); } while (0)
+#define RSB_STAMP_T(k, t) do { if (g_timeline && tid == (t)) g_timeline[((size_t)img * 2 + rank) * 96 + (k)] = clock64(); } while (0)
+#define RSB_STAMP(k) do { if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 96 + (k)] = clock64(); } while (0)
 #else
 #define RSB_STAMP(k) do {} while (0)
 #define RSB_STAMP_T(k, t) do {} while (0)
+#endif
+#ifdef RSB_DBG_NOEX2  // experiment: phase 1 without the SFU (wrong images)
+#define P1_EX2(x) (x)
+#else
+#define P1_EX2(x) ex2(x)
 #endif
 
 constexpr int kWorkers = 512;             // threads that render
@@ -49,11 +54,29 @@ constexpr int kRowsPerWarp = kMaxBand / kWarps;
 constexpr int kMaxGroups = kMaxBand / kTileRows;
 constexpr int kMaxCand = 64;
 constexpr int kMaxTiles = kMaxGroups * 4;  // 64-column tiles of a band (size <= 256)
+constexpr int kMaxRec = 8;                 // tiles per warp and image (work list length)
+constexpr unsigned kRecEnd = 0xffffu;      // list terminator in rec.y
+
+// float32 coefficients of one live component as the tile loop reads them (warp-uniform):
+//   g(r,c) = 2^(la + A dc^2 + B dc dr + C dr^2),  dc = c - (icf + fc), dr = r - (irf + fr)
+// Rows are rendered in blocks of four from two exponentials per column,
+//   E(i) = E0 U^i 2^(C (i^2 - i)),  E0 = g(r_b, c),  U = 2^(B dc + 2 C dr_b + C),
+// so k2 = 2^(2C) and k3 = 2^(6C) ride along.  Components this does not suit (amplitude <= 0,
+// sigma below ~0.6 pixel, non-finite numbers) carry k2 < 0 and la = the amplitude itself:
+// they take one exponential per pixel.
+struct __align__(16) Coef2 {
+  float A, B, C, la;
+  float irf, fr, icf, fc;  // centre split into integer part and fraction
+  float k2, k3;
+  int r0, r1, c0, c1;      // inclusive bounding box of the > tau footprint (builder only)
+  int pad[2];
+};
+static_assert(sizeof(Coef2) == 64, "Coef2 layout");
 
 struct __align__(16) Fixed2 {
   double params[3][kMaxSlots * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
-  Coef coef[2][kMaxSlots];                             // double buffered, built one image ahead
-  int span[2][kMaxSlots][kMaxGroups];  // lo | hi << 16 column interval per (live slot, row group)
+  Coef2 coef[2][kMaxSlots];                            // double buffered, built one image ahead
+  int hist[32];                     // build_coefs2 scratch: tiles per cost
   double pix64[20 * kMaxSlots];     // peak64 scratch: 16 pixel x slot terms + 4 per-slot rotations
   uint64_t bar[3];
   unsigned long long xval[3][2];    // peer's margin / (unused) / arg-max key, [kind][use parity]
@@ -61,16 +84,15 @@ struct __align__(16) Fixed2 {
   unsigned long long lbest;         // this CTA's running arg-max key
   int lmargin;                      // this CTA's running margin
   int nlive[2];
-  int next_tile;
   int next_row;
   int foot_lo, foot_hi;             // output coordinates with a non-zero tap
   float delta[2];
   int dlo[2];                       // no pixel closer than this to the border exceeds 0.01
   struct LabelReq { unsigned long long best; int img, pb, margin, zpad; } label[2];  // [image parity]
-  float geo[kMaxSlots * 8];         // build_coefs2 scratch (SlotGeo per live slot)
+  float geo[kMaxSlots * 16];        // build_coefs2 scratch (SlotGeo per live slot)
   int ncand;                        // borderline pixels awaiting a float64 verdict
   int cand[kMaxCand];               // r << 16 | c
-  unsigned char tile_order[kMaxTiles];  // tiles sorted by distance from the image centre
+  uint2 rec[2][kWarps][kMaxRec];    // per-warp work lists: {slots that touch the tile, row group << 8 | column tile}
 };
 
 // one slot's float64 value at a raw pixel, operation order of gauss.py:77-88
@@ -85,6 +107,13 @@ __device__ inline double gauss64(const double* p, int r, int c) {
   const double a = (ra - ua) / p[4];
   const double b = (rb - ub) / p[3];
   return amp * exp(-(a * a + b * b) / 2.0);
+}
+
+// Index of the lowest set bit without FLO/POPC (those are SFU-queue instructions and would
+// wait behind the exponentials): isolate the bit, convert to float on the FMA pipe, read the
+// exponent.  Negative for x == 0.
+__device__ __forceinline__ int lowest_bit(unsigned x) {
+  return (int)(__float_as_uint(__uint2float_rn(x & (0u - x))) >> 23) - 127;
 }
 
 __device__ __forceinline__ unsigned long long best_key(float v, int idx) {
@@ -118,34 +147,52 @@ __device__ __forceinline__ void store_out4(char* out_row, bool f64, int c0, int 
   }
 }
 
-// ---- one warp: parameter block -> compacted coefficients + culling spans + dlo ---------
-// Runs while the other warps render the previous image, so it is written for latency:
-// float32 throughout (only the centre split needs the float64 parameters) and every lane
-// busy.  Ellipse of the > tau footprint: z^T M z <= T^2 with z = (dr, dc).  For a row range
-// the covered columns are [min cl, max cr], cl/cr = centre line -/+ half width; cr is
-// concave in dr, so its maximum over the range is the ellipse's rightmost point if that
-// row lies in the range, else the larger end value (mirror image for cl).
-struct SlotGeo {  // per live slot, shared between the lanes through shared memory
-  float Mrr, Mcc, Mrc, T2, ec, x, y;
+// ---- one warp: parameter block -> compacted coefficients + per-warp work lists + dlo -----
+// Runs while the other warps render the previous image, so it is written for latency: float32
+// throughout (only the centre split needs the float64 parameters), every lane busy, and as
+// few SFU-queue round trips as possible (divisions, square roots, float->int conversions,
+// FLO and POPC all queue behind the renderers' exponentials).
+// Ellipse of the > tau footprint: z^T M z <= T^2 with z = (dr, dc).  For a row range the
+// covered columns are [min cl, max cr], cl/cr = centre line -/+ half width; cr is concave in
+// dr, so its maximum over the range is the ellipse's rightmost point if that row lies in the
+// range, else the larger end value (mirror image for cl).
+struct __align__(16) SlotGeo {  // per live slot, shared between the lanes through shared memory
+  float Mrr, Mcc, Mrc, T2;
+  float ec, x, y, det;
+  float inv_cc, inv_rr, pad0;
   int degenerate;
+  float ka, kx, ky, pad;  // frame bound: amplitude and 1-D decay rates (log2 units)
 };
+static_assert(sizeof(SlotGeo) == 64, "SlotGeo layout");
 
+// round to nearest on the FMA pipe (|x| < 2^22); the callers widen by one pixel instead of
+// asking for floor / ceil
+__device__ __forceinline__ int round_fma(float x) {
+  return __float_as_int(fminf(fmaxf(x, -4.0e6f), 4.0e6f) + 12582912.f) - 0x4B400000;
+}
+
+#ifdef RSB_TIMELINE
+#define RSB_BSTAMP(k) do { if (dbg_tl && lane == 0) dbg_tl[k] = clock64(); } while (0)
+#else
+#define RSB_BSTAMP(k) do {} while (0)
+#endif
 __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
-                                    int H, int lane, bool zoom) {
+                                    int H, int lane, bool zoom, long long* dbg_tl = nullptr) {
+  RSB_BSTAMP(0);
   SlotGeo* geo = reinterpret_cast<SlotGeo*>(sm.geo);
   float amax = 0.f;
   for (int k = lane; k < slots; k += 32) amax = fmaxf(amax, fabsf((float)P[k * 6]));
   amax = warp_max(amax);
   const float tau = 2e-8f * amax;  // <= 19 x 2e-8 of the peak is dropped in total
   const int ngroups = (H + kTileRows - 1) / kTileRows;
+  const int tcols = (N + kTileCols - 1) / kTileCols, ntiles = ngroups * tcols;
+  sm.hist[lane] = 0;
   int base = 0;
-  // frame bound (dlo) inputs of this lane's slots: k = lane, lane + 32
-  float ka[2] = {0.f, 0.f}, kx[2] = {0.f, 0.f}, ky[2] = {0.f, 0.f}, cx[2] = {0.f, 0.f}, cy[2] = {0.f, 0.f};
   bool certified = false, all_nonneg = true;
-  for (int k0 = 0, h = 0; k0 < slots; k0 += 32, ++h) {
+  for (int k0 = 0; k0 < slots; k0 += 32) {
     const int k = k0 + lane;
     bool live = false;
-    Coef c;
+    Coef2 c;
     SlotGeo g;
     g.degenerate = 0;
     if (k < slots) {
@@ -163,7 +210,13 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
         c.A = -hl * g.Mcc;
         c.C = -hl * g.Mrr;
         c.B = -2.f * hl * g.Mrc;
-        c.amp = amp;
+        {
+          const bool blocks = amp > 0.f && c.C >= -2.f && isfinite(c.A) && isfinite(c.B) && isfinite(c.C);
+          c.la = blocks ? log2f(amp) : amp;
+          c.k2 = blocks ? exp2f(2.f * c.C) : -1.f;
+          c.k3 = blocks ? exp2f(6.f * c.C) : -1.f;
+          c.pad[0] = c.pad[1] = 0;
+        }
         const double yr = rint(yd), xr = rint(xd);
         c.irf = (float)yr;
         c.fr = (float)(yd - yr);
@@ -172,10 +225,14 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
         g.x = (float)xd;
         g.y = (float)yd;
         g.T2 = 2.f * logf(fabsf(amp) / tau);
-        const float det = g.Mrr * g.Mcc - g.Mrc * g.Mrc;
-        const float er = sqrtf(g.T2 * g.Mcc / det);
-        g.ec = sqrtf(g.T2 * g.Mrr / det);
+        g.det = g.Mrr * g.Mcc - g.Mrc * g.Mrc;
+        const float inv_det = 1.f / g.det, inv_rr = 1.f / g.Mrr;
+        g.inv_cc = 1.f / g.Mcc;
+        const float er = sqrtf(g.T2 * g.Mcc * inv_det);
+        g.ec = sqrtf(g.T2 * g.Mrr * inv_det);
         g.degenerate = !(isfinite(er) && isfinite(g.ec));
+        g.inv_rr = inv_rr;
+        g.pad0 = 0.f;
         const float lo_r = fmaxf(floorf(g.y - er) - 1.f, 0.f), hi_r = fminf(ceilf(g.y + er) + 1.f, N - 1.f);
         const float lo_c = fmaxf(floorf(g.x - g.ec) - 1.f, 0.f), hi_c = fminf(ceilf(g.x + g.ec) + 1.f, N - 1.f);
         if (g.degenerate) {
@@ -185,22 +242,18 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
           live = true;
           c.r0 = (int)lo_r; c.r1 = (int)hi_r; c.c0 = (int)lo_c; c.c1 = (int)hi_c;
         }
-        if (h < 2) {
-          ka[h] = fabsf(amp) * 1.0001f;
-          kx[h] = (det / g.Mrr) * 0.9999f * hl;
-          ky[h] = (det / g.Mcc) * 0.9999f * hl;
-          cx[h] = g.x;
-          cy[h] = g.y;
-          // the pixel nearest to the centre is at most half a pixel away in each coordinate:
-          // this slot alone lifts it above the threshold -> the > 0.01 mask is not empty
-          const float qmax = 0.25f * (g.Mrr + g.Mcc + 2.f * fabsf(g.Mrc));
-          if (amp * __expf(-0.5f * qmax) > 0.0101f && g.x >= 0.f && g.x <= N - 1.f && g.y >= 0.f &&
-              g.y <= N - 1.f)
-            certified = true;
-        }
+        g.ka = fabsf(amp) * 1.0001f;
+        g.kx = (g.det * inv_rr) * 0.9999f * hl;
+        g.ky = (g.det * g.inv_cc) * 0.9999f * hl;
+        g.pad = 0.f;
+        // the pixel nearest to the centre is at most half a pixel away in each coordinate:
+        // this slot alone lifts it above the threshold -> the > 0.01 mask is not empty
+        const float qmax = 0.25f * (g.Mrr + g.Mcc + 2.f * fabsf(g.Mrc));
+        if (amp * __expf(-0.5f * qmax) > 0.0101f && g.x >= 0.f && g.x <= N - 1.f && g.y >= 0.f &&
+            g.y <= N - 1.f)
+          certified = true;
       }
       if (p[0] < 0.0) all_nonneg = false;
-      if (p[0] != 0.0 && h >= 2) all_nonneg = false;  // > 64 slots: no frame bound
     }
     const unsigned mask = __ballot_sync(0xffffffffu, live);
     if (live) {
@@ -211,79 +264,126 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
     base += __popc(mask);
   }
   __syncwarp();
-  // culling spans: (slot, row group) pairs dealt over the lanes
-  for (int e = lane; e < base * ngroups; e += 32) {
-    const int pos = e / ngroups, gi = e - pos * ngroups;
-    const SlotGeo g = geo[pos];
-    const Coef& c = sm.coef[cb][pos];
-    const int ga = max(R0 + gi * kTileRows, c.r0);
-    const int gb = min(min(R0 + gi * kTileRows + kTileRows - 1, R0 + H - 1), c.r1);
-    int packed = 0x7fff;  // lo = 32767 > hi = 0: empty
-    if (ga <= gb) {
-      int lo_i = c.c0, hi_i = c.c1;
-      if (!g.degenerate) {
-        const float det = g.Mrr * g.Mcc - g.Mrc * g.Mrc;
-        const float dr_right = -g.Mrc * g.ec / g.Mrr;  // row offset of the rightmost point
-        const float inv_cc = 1.f / g.Mcc, slope = -g.Mrc * inv_cc;
-        const float da = (float)ga - g.y, db = (float)gb - g.y;
-        const float hwa = sqrtf(fmaxf(g.T2 * g.Mcc - det * da * da, 0.f)) * inv_cc;
-        const float hwb = sqrtf(fmaxf(g.T2 * g.Mcc - det * db * db, 0.f)) * inv_cc;
-        const float cla = slope * da, clb = slope * db;
-        const float hi = (da <= dr_right && dr_right <= db) ? g.ec : fmaxf(cla + hwa, clb + hwb);
-        const float lo = (da <= -dr_right && -dr_right <= db) ? -g.ec : fminf(cla - hwa, clb - hwb);
-        lo_i = max((int)floorf(g.x + lo) - 1, c.c0);
-        hi_i = min((int)ceilf(g.x + hi) + 1, c.c1);
-      }
-      if (lo_i <= hi_i) packed = lo_i | (hi_i << 16);
-    }
-    sm.span[cb][pos][gi] = packed;
-  }
+  RSB_BSTAMP(1);
+  RSB_BSTAMP(2);
   // Zoom images only use the crop [margin, N-margin)^2 of the raw image, and margin >= dlo,
-  // where dlo is the smallest border distance d at which an UPPER BOUND of the image over
-  // the frame {border distance <= d} exceeds the 0.01 threshold.  Bound: sum over slots of
-  // the slot's maximum over the frame = amp if its centre lies in the frame, else
-  // amp * exp(-q/2) with q the smallest Mahalanobis distance to the four frame lines.
+  // where dlo is a border distance d such that an UPPER BOUND of the image over the frame
+  // {border distance <= d - 1} stays below the 0.01 threshold.  Bound: sum over slots of the
+  // slot's maximum over the frame = amp if its centre lies in the frame, else amp * exp(-q/2)
+  // with q the smallest Mahalanobis distance to the four frame lines.  The bound grows with d:
+  // 32 frames are tried at once, one per lane (dlo only feeds the tile skip, a multiple of
+  // `step` is as good as the exact value).
   int dlo = 0;
   if (zoom) {
     certified = __any_sync(0xffffffffu, certified) && __all_sync(0xffffffffu, all_nonneg);
-    auto frame_bound = [&](int d) -> float {
+    // without the certificate an empty mask (margin := 0, whole image used) cannot be ruled out
+    if (certified) {
+      const int half = (N - 1) / 2, step = (half + 31) / 32;
+      const int d = step * lane + step - 1;
       const float lo = (float)d, hi = (float)(N - 1 - d);
       float u = 0.f;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        if (ka[h] == 0.f) continue;
-        float v = ka[h];
-        if (!(cx[h] <= lo || cx[h] >= hi || cy[h] <= lo || cy[h] >= hi)) {
-          const float dc0 = lo - cx[h], dc1 = hi - cx[h], dr0 = lo - cy[h], dr1 = hi - cy[h];
-          const float q = fminf(fminf(dc0 * dc0, dc1 * dc1) * kx[h], fminf(dr0 * dr0, dr1 * dr1) * ky[h]);
-          v *= ex2(-q);
-        }
-        u += v;
+#pragma unroll 4
+      for (int pos = 0; pos < base; ++pos) {  // branch-free: the exponentials of a batch overlap
+        const float4 gx = *reinterpret_cast<const float4*>(&geo[pos].ec);   // ec x y det
+        const float4 gk = *reinterpret_cast<const float4*>(&geo[pos].ka);   // ka kx ky -
+        const bool in_frame = gx.y <= lo || gx.y >= hi || gx.z <= lo || gx.z >= hi;
+        const float dc0 = lo - gx.y, dc1 = hi - gx.y, dr0 = lo - gx.z, dr1 = hi - gx.z;
+        const float q = fminf(fminf(dc0 * dc0, dc1 * dc1) * gk.y, fminf(dr0 * dr0, dr1 * dr1) * gk.z);
+        u += gk.x * ex2(in_frame ? 0.f : -q);
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
-      return u;
-    };
-    const float limit = 0.00999f;
-    // without the certificate an empty mask (margin := 0, whole image used) cannot be ruled out
-    if (certified && frame_bound(0) <= limit) {
-      int a_ = 0, b_ = (N - 1) / 2;
-      if (frame_bound(b_) <= limit) {
-        a_ = -1;  // cannot happen with a certificate; stay safe
-      } else {
-        while (b_ - a_ > 1) {
-          const int mid = (a_ + b_) >> 1;
-          if (frame_bound(mid) <= limit) a_ = mid; else b_ = mid;
-        }
-      }
-      dlo = a_ + 1;  // frames 0..a_ hold nothing above the threshold
+      const unsigned okm = __ballot_sync(0xffffffffu, d <= half && u <= 0.00999f);
+      const unsigned bad = ~okm;
+      const int lead = bad ? lowest_bit(bad) : 32;  // leading frames that hold nothing above the threshold
+      dlo = (lead == 32) ? 0 : step * lead;         // (all 32 below: cannot happen with a certificate; stay safe)
     }
   }
   if (lane == 0) {
     sm.nlive[cb] = base;
-    sm.delta[cb] = 2e-6f * fmaxf(1.f, amax);
+    sm.delta[cb] = 6e-6f * fmaxf(1.f, amax);
     sm.dlo[cb] = dlo;
   }
+  RSB_BSTAMP(3);
+  // ---- static work lists -------------------------------------------------------------
+  // Every tile's set of overlapping slots is known here, one image ahead of its use, so the
+  // tiles are dealt to the warps now: sorted by cost (slots hit), heaviest first, in snake
+  // order.  The renderers then read their list with plain loads -- no queue, no atomics, no
+  // shuffles on their critical path.  Warps 0 and 1 (side jobs) receive none.
+  {
+    uint2* rec = &sm.rec[cb][0][0];
+    for (int e = lane; e < kWarps * kMaxRec; e += 32) rec[e] = make_uint2(0u, kRecEnd);
+    __syncwarp();
+    unsigned hits[2] = {0u, 0u};
+    int cost[2] = {0, 0}, tag[2] = {0, 0}, among[2] = {0, 0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int u = lane + 32 * h;
+      if (u < ntiles) {
+        const unsigned inv_tc = (65536u + (unsigned)tcols - 1u) / (unsigned)tcols;
+        const int g = (int)(((unsigned)u * inv_tc) >> 16), tc = u - g * tcols;
+        const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols;
+        const int rend = min(R0 + H, r0 + kTileRows);
+        // every pixel of the tile closer than dlo to the border: never read, never above 0.01
+        // (two pixels of slack: zero-weight taps may touch the crop's neighbours)
+        const int rmid = min(max(N >> 1, r0), rend - 1), cmid = min(max(N >> 1, tc0), min(tc0 + kTileCols, N) - 1);
+        const int far = min(min(rmid, N - 1 - rmid), min(cmid, N - 1 - cmid));
+        if (!(zoom && far < dlo - 2)) {
+          // a slot touches the tile when its > tau ellipse  M[dr,dc] <= T^2  meets the tile's
+          // rectangle (1.5 pixels of slack): the form's minimum over a box that does not hold
+          // the centre lies on one of the four edges.  No square roots, no divisions.
+          const float ra = (float)r0 - 1.5f, rb = (float)(rend - 1) + 1.5f;
+          const float ca = (float)tc0 - 1.5f, cb_ = (float)(min(tc0 + kTileCols, N) - 1) + 1.5f;
+          unsigned m = 0u;
+#pragma unroll 4
+          for (int pos = 0; pos < base; ++pos) {  // branch-free: the loads of a batch overlap
+            const int2 bbr = *reinterpret_cast<const int2*>(&sm.coef[cb][pos].r0);  // r0 r1
+            const int2 bbc = *reinterpret_cast<const int2*>(&sm.coef[cb][pos].c0);  // c0 c1
+            const int4 bb = make_int4(bbr.x, bbr.y, bbc.x, bbc.y);
+            const float4 gm = *reinterpret_cast<const float4*>(&geo[pos].Mrr);     // Mrr Mcc Mrc T2
+            const float4 gx = *reinterpret_cast<const float4*>(&geo[pos].ec);      // ec x y det
+            const float4 gi = *reinterpret_cast<const float4*>(&geo[pos].inv_cc);  // inv_cc inv_rr - -
+            const bool inbox = !(bb.y < r0 || bb.x >= rend || bb.w < tc0 || bb.z >= tc0 + kTileCols);
+            const float dra = ra - gx.z, drb = rb - gx.z, dca = ca - gx.y, dcb = cb_ - gx.y;
+            // only the edges that face the centre can hold the minimum
+            const bool use_c = dca > 0.f || dcb < 0.f, use_r = dra > 0.f || drb < 0.f;
+            const float e = dca > 0.f ? dca : dcb, f = dra > 0.f ? dra : drb;
+            const float tc_ = fminf(fmaxf(-gm.z * e * gi.y, dra), drb);  // column edge dc = e, dr free
+            const float qc = (gm.x * tc_ + 2.f * gm.z * e) * tc_ + gm.y * e * e;
+            const float tr_ = fminf(fmaxf(-gm.z * f * gi.x, dca), dcb);  // row edge dr = f, dc free
+            const float qr = (gm.y * tr_ + 2.f * gm.z * f) * tr_ + gm.x * f * f;
+            const float big = 3.0e38f;
+            float qmin = fminf(use_c ? qc : big, use_r ? qr : big);
+            if (!use_c && !use_r) qmin = 0.f;  // the centre lies inside the rectangle
+            // (NaN from a degenerate slot counts as touching)
+            if (inbox && !(qmin > gm.w)) m |= 1u << pos;
+          }
+          hits[h] = m;
+          cost[h] = 1 + min(__popc(hits[h]), 30);
+          tag[h] = (g << 8) | tc;
+          among[h] = atomicAdd(&sm.hist[cost[h]], 1);  // position among the tiles of equal cost
+        }
+      }
+    }
+    __syncwarp();
+    // rank = tiles of higher cost + position among equals
+    int above[2] = {0, 0};
+    for (int c = 31; c >= 1; --c) {
+      const int n = sm.hist[c];
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+        if (c > cost[h]) above[h] += n;
+    }
+    // Snake deal over the 14 warps without a side job.
+    constexpr int kSeats = kWarps - 2;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (cost[h] == 0) continue;
+      const int i = above[h] + among[h];
+      const int ps = i / kSeats, j = i - ps * kSeats;
+      const int w = 2 + ((ps & 1) ? j : kSeats - 1 - j), e = ps;
+      sm.rec[cb][w][e] = make_uint2(hits[h], (unsigned)tag[h]);
+    }
+  }
+  RSB_BSTAMP(4);
 }
 
 // ---- float64 peak (jet_max) for the labels, one warp -------------------------------
@@ -394,11 +494,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const uint32_t s_raw = keep_u32(smem_u32(raw)), s_tabw = keep_u32(smem_u32(tab_w)),
                  s_tabi = keep_u32(smem_u32(tab_i));
   const int tid = keep_s32((int)threadIdx.x), lane = tid & 31, warp = tid >> 5;
-  const int rank = (kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0;
+  const int rank = keep_s32((kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0);
   const int cid = blockIdx.x / kCluster, nclusters = gridDim.x / kCluster;
   const int H = N / kCluster;                // rows of this CTA's band (N even when kCluster == 2)
-  const int R0 = rank * H;                   // first absolute row of the band
-  const int base = (rank == 0) ? 0 : H - 1;  // absolute row stored at raw row 0 (rank 1: halo)
+  const int R0 = keep_s32(rank * H);                   // first absolute row of the band
+  const int base = keep_s32((rank == 0) ? 0 : H - 1);  // absolute row stored at raw row 0 (rank 1: halo)
   // remote (peer CTA) shared-memory addresses for st.async
   uint32_t peer_xval = 0, peer_xbar = 0, peer_raw = 0;
   if constexpr (kCluster > 1) {
@@ -426,7 +526,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
   const int strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
   const int tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
-  const int ntiles = ((H + kTileRows - 1) / kTileRows) * tcols;
   const bool vec = (N & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
@@ -445,21 +544,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     fence_mbar_init();
     sm.lmargin = N;
     sm.lbest = 0ull;
-    sm.next_tile = 0;
     sm.next_row = 0;
-  }
-  // tile visiting order: by distance of the tile centre from the image centre, so that the
-  // heavy central tiles are dealt first and the dynamic schedule ends on light ones
-  for (int t = tid; t < ntiles; t += kWorkers) {
-    auto key = [&](int u) {
-      const int gg = u / tcols, cc = u - gg * tcols;
-      const int dy = 2 * (R0 + gg * kTileRows) + kTileRows - N, dx = 2 * cc * kTileCols + kTileCols - N;
-      return (dy * dy + dx * dx) * 256 + u;  // unique
-    };
-    const int mykey = key(t);
-    int pos = 0;
-    for (int u = 0; u < ntiles; ++u) pos += key(u) < mykey;
-    sm.tile_order[pos] = (unsigned char)t;
   }
   __syncthreads();
   auto prefetch = [&](int image, int pb) {  // one thread: parameter block -> params[pb]
@@ -513,8 +598,13 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         if (img + nclusters < a.n) {
           const int nb = (it + 1) % 3;
           mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
+#ifdef RSB_TIMELINE
+          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane, a.zoom_pad[img + nclusters] >= 0,
+                       g_timeline ? &g_timeline[((size_t)img * 2 + rank) * 96 + 24] : nullptr);
+#else
           build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane,
                        a.zoom_pad[img + nclusters] >= 0);
+#endif
         }
         RSB_STAMP_T(12, kCoefWarp * 32);
       } else if (warp == kLabelWarp) {
@@ -529,107 +619,219 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const int zpad = zpad_next;
     if (img + nclusters < a.n) zpad_next = a.zoom_pad[img + nclusters];  // latency hidden
     const bool zoom = zpad >= 0;
-    const int nlive = sm.nlive[buf];
     const float thr = (float)kEdgeThr, delta = sm.delta[buf];
-    const int dlo = sm.dlo[buf];
-    const uint32_t s_coef = keep_u32(smem_u32(sm.coef[buf])), s_span = keep_u32(smem_u32(sm.span[buf]));
+    const uint32_t s_coef = keep_u32(smem_u32(sm.coef[buf]));
+    const uint32_t pitch4 = keep_u32((uint32_t)pitch * 4u);
 
     // ---------------- phase 1: splat this CTA's band, 8 x 64 tiles ------------------
+    // Each warp walks its own work list (built one image ahead by build_coefs2).  Everything
+    // that comes out of shared memory is requested one step before it is needed -- the next
+    // tile's record during this tile, the next slot's coefficients during this slot -- because
+    // a shared-memory round trip queues behind the other warps' MUFU work.
     int my_margin = N;
     unsigned long long my_best = 0ull;
     float best_v = -1.f;
-    const float inv_tcols = 1.f / (float)tcols;
-    for (;;) {
-      int t = 0;
-      if (lane == 0) t = atomicAdd(&sm.next_tile, 1);
-      t = __shfl_sync(0xffffffffu, t, 0);
-      if (t >= ntiles) break;
-      const int ta = sm.tile_order[t];  // central (heavy) tiles first, light corners last
-      const int g = __float2int_rz(((float)ta + 0.5f) * inv_tcols), tc = ta - g * tcols;
+#ifdef RSB_TIMELINE
+    long long dbg_t0 = clock64(), dbg_hit = 0, dbg_epi = 0, dbg_ntile = 0, dbg_nhit = 0;
+    const long long dbg_start = dbg_t0;
+#define DBG_LAP(acc) do { const long long _n = clock64(); acc += _n - dbg_t0; dbg_t0 = _n; } while (0)
+#else
+#define DBG_LAP(acc) do {} while (0)
+#endif
+    const uint32_t s_rec = keep_u32(smem_u32(&sm.rec[buf][warp][0]));
+    const float tl = thr - delta, th = thr + delta;
+    uint2 rc = lds_v2u(s_rec);
+    // coefficients of the slot about to be rendered
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f), ct = q;
+    float2 kk = make_float2(0.f, 0.f);
+    auto load_first = [&](const uint2& r) {
+      if (r.y != kRecEnd && r.x) {
+        const uint32_t an = s_coef + (uint32_t)lowest_bit(r.x) * 64u;
+        q = lds_v4(an);         // A B C la
+        ct = lds_v4(an + 16u);  // irf fr icf fc
+        kk = lds_v2(an + 32u);  // k2 k3
+      }
+    };
+    load_first(rc);
+    for (int e = 0; rc.y != kRecEnd; ++e) {
+      uint2 nx = make_uint2(0u, kRecEnd);
+      if (e + 1 < kMaxRec) nx = lds_v2u(s_rec + (uint32_t)(e + 1) * 8u);
+      const int g = (int)(rc.y >> 8), tc = (int)(rc.y & 0xffu);
       const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
       const uint32_t s_dst = s_raw + (uint32_t)((r0 - base) * pitch + c0) * 4u;
       const int rend = min(R0 + H, r0 + kTileRows);  // rows of this tile that exist
-      {
-        // every pixel of the tile closer than dlo to the border: never read, never above 0.01
-        const int rmid = min(max(N >> 1, r0), rend - 1), cmid = min(max(N >> 1, tc0), min(tc0 + kTileCols, N) - 1);
-        const int far = min(min(rmid, N - 1 - rmid), min(cmid, N - 1 - cmid));
-        // (two pixels of slack: zero-weight taps may touch the crop's neighbours)
-        if (zoom && far < dlo - 2) continue;
-      }
       const float r0f = (float)r0, c0f = (float)c0;
+#ifdef RSB_TIMELINE
+      dbg_ntile++;
+      dbg_nhit += __popc(rc.x);
+#endif
       f2 acc2[kTileRows];  // two adjacent pixels per row, packed (FFMA2)
 #pragma unroll
       for (int i = 0; i < kTileRows; ++i) acc2[i] = 0ull;
-      // cull: lane k tests live slot k (and k+32) against the tile, the warp walks the hits
-      for (int k0 = 0; k0 < nlive; k0 += 32) {
-        bool hit = false;
-        if (k0 + lane < nlive) {
-          const int sp = lds_s32(s_span + (uint32_t)((k0 + lane) * kMaxGroups + g) * 4u);
-          hit = !((sp >> 16) < tc0 || (sp & 0xffff) > tc0 + kTileCols - 1);
-        }
-        unsigned hits = __ballot_sync(0xffffffffu, hit);
-        while (hits) {
-          const int k = k0 + __ffs(hits) - 1;
-          hits &= hits - 1;
-          const float4 q = lds_v4(s_coef + (uint32_t)k * 48u);        // A B C amp
-          const float4 ct = lds_v4(s_coef + (uint32_t)k * 48u + 16u);  // irf fr icf fc
-          const float d0 = (c0f - ct.z) - ct.w;
-          const f2 d = f2_pack(d0, d0 + 1.f);
-          const f2 Q = f2_mul(f2_pack(q.y, q.y), d);
-          const f2 Pq = f2_mul(f2_mul(f2_pack(q.x, q.x), d), d);
-          const f2 amp2 = f2_pack(q.w, q.w);
-          const float dr0 = (r0f - ct.x) - ct.y;
+      // one slot over this lane's 16 pixels of the tile
+      auto slot_math = [&](const float4& cq, const float4& cc, const float2& ck) {
+        const float d0 = (c0f - cc.z) - cc.w;
+        const f2 d = f2_pack(d0, d0 + 1.f);
+        const f2 Q = f2_mul(f2_pack(cq.y, cq.y), d);
+        const float dr0 = (r0f - cc.x) - cc.y;
+        if (ck.x > 0.f) {
+          // rows in two blocks of four, two exponentials per column and block (see Coef2)
+          const f2 Pq = f2_fma(f2_mul(f2_pack(cq.x, cq.x), d), d, f2_pack(cq.w, cq.w));  // A dc^2 + la
+          const f2 k2 = f2_pack(ck.x, ck.x), k3 = f2_pack(ck.y, ck.y);
+#pragma unroll
+          for (int b = 0; b < kTileRows; b += 4) {
+            const float dr = dr0 + (float)b;
+            const float Cq = cq.z * dr * dr;
+            const float tw = fmaf(2.f * cq.z, dr, cq.z);  // 2 C dr + C
+            float ta, tb, wa, wb;
+            f2_unpack(f2_fma(f2_pack(dr, dr), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
+            f2_unpack(f2_add(Q, f2_pack(tw, tw)), wa, wb);
+            // (the clamp never binds where the block holds a pixel above the cut-off, sigma >=
+            // 0.6: there |w| < 31; elsewhere it keeps U^3 finite)
+            const f2 E0 = f2_pack(P1_EX2(ta), P1_EX2(tb));
+            const f2 U = f2_pack(P1_EX2(fminf(wa, 40.f)), P1_EX2(fminf(wb, 40.f)));
+            const f2 U2 = f2_mul(U, U);
+            acc2[b] = f2_add(acc2[b], E0);
+            acc2[b + 1] = f2_fma(E0, U, acc2[b + 1]);
+            acc2[b + 2] = f2_fma(E0, f2_mul(U2, k2), acc2[b + 2]);
+            acc2[b + 3] = f2_fma(E0, f2_mul(f2_mul(U2, U), k3), acc2[b + 3]);
+          }
+        } else {
+          // one exponential per pixel; cq.w holds the amplitude itself
+          const f2 Pq = f2_mul(f2_mul(f2_pack(cq.x, cq.x), d), d);
+          const f2 amp2 = f2_pack(cq.w, cq.w);
 #pragma unroll
           for (int i = 0; i < kTileRows; i += 2) {
             // two rows at a time: dr and C dr^2 as a packed pair, then broadcast per row
             const f2 drp = f2_pack(dr0 + (float)i, dr0 + (float)(i + 1));
-            const f2 Cqp = f2_mul(f2_mul(f2_pack(q.z, q.z), drp), drp);
+            const f2 Cqp = f2_mul(f2_mul(f2_pack(cq.z, cq.z), drp), drp);
             float dra, drb, Cqa, Cqb;
             f2_unpack(drp, dra, drb);
             f2_unpack(Cqp, Cqa, Cqb);
             float ta, tb;
             f2_unpack(f2_fma(f2_pack(dra, dra), Q, f2_add(Pq, f2_pack(Cqa, Cqa))), ta, tb);
-            acc2[i] = f2_fma(amp2, f2_pack(ex2(ta), ex2(tb)), acc2[i]);
+            acc2[i] = f2_fma(amp2, f2_pack(P1_EX2(ta), P1_EX2(tb)), acc2[i]);
             f2_unpack(f2_fma(f2_pack(drb, drb), Q, f2_add(Pq, f2_pack(Cqb, Cqb))), ta, tb);
-            acc2[i + 1] = f2_fma(amp2, f2_pack(ex2(ta), ex2(tb)), acc2[i + 1]);
+            acc2[i + 1] = f2_fma(amp2, f2_pack(P1_EX2(ta), P1_EX2(tb)), acc2[i + 1]);
           }
         }
+      };
+      // The next slot's coefficients are requested before this slot's arithmetic (slot 0 when
+      // there is none: always valid memory, never used).  The warp barrier pins the loads above
+      // the arithmetic: ptxas otherwise sinks them to the end of the iteration, where their
+      // latency is exposed.  Unrolled by two so that the two coefficient sets swap roles
+      // without register moves.
+      unsigned rest = rc.x;  // slots still to render; the lowest one's coefficients are in q, ct, kk
+      float4 qb, cb;
+      float2 kb;
+      while (rest) {
+        rest &= rest - 1;
+        {
+          const uint32_t an = s_coef + (uint32_t)max(lowest_bit(rest), 0) * 64u;
+          qb = lds_v4(an);
+          cb = lds_v4(an + 16u);
+          kb = lds_v2(an + 32u);
+        }
+        __syncwarp();
+        slot_math(q, ct, kk);
+        if (!rest) break;
+        rest &= rest - 1;
+        {
+          const uint32_t an = s_coef + (uint32_t)max(lowest_bit(rest), 0) * 64u;
+          q = lds_v4(an);
+          ct = lds_v4(an + 16u);
+          kk = lds_v2(an + 32u);
+        }
+        __syncwarp();
+        slot_math(qb, cb, kb);
       }
+      load_first(nx);  // in flight during the epilogue
       float acc[kTileRows][2];
 #pragma unroll
       for (int i = 0; i < kTileRows; ++i) f2_unpack(acc2[i], acc[i][0], acc[i][1]);
+      DBG_LAP(dbg_hit);
       if (c0 < N) {
         float tile_top = 0.f;
+        const bool full = r0 + kTileRows <= rend;  // always, when the band is a multiple of 8 rows
+        if (full) {
 #pragma unroll
-        for (int i = 0; i < kTileRows; ++i) {
-          if (r0 + i < rend) {
-            sts_v2(s_dst + (uint32_t)(i * pitch) * 4u, acc[i][0], acc[i][1]);
+          for (int i = 0; i < kTileRows; ++i) {
+            sts_v2(s_dst + (uint32_t)i * pitch4, acc[i][0], acc[i][1]);
             tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < kTileRows; ++i) {
+            if (r0 + i < rend) {
+              sts_v2(s_dst + (uint32_t)i * pitch4, acc[i][0], acc[i][1]);
+              tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
+            }
           }
         }
         if (zoom) {
           // border distance of this lane's nearest-to-border pixel in the tile
           const int rl = rend - 1;
           const int dmin = min(min(r0, N - 1 - rl), min(c0, N - 1 - min(c0 + 1, N - 1)));
-          if (tile_top > thr - delta && dmin < my_margin) {
+          if (tile_top > tl && dmin < my_margin) {
+            // The border distance of pixel (r, c) is min(db(r), dc(c)), so its minimum over the
+            // pixels above the threshold splits into "first row with a pixel above" and "first
+            // column with a pixel above" -- when the tile lies on one side of both centre
+            // lines, rows and columns are monotone in border distance.
+            const bool top = 2 * (r0 + kTileRows - 1) <= N - 1, bottom = 2 * r0 >= N - 1;
+            const bool left = 2 * (c0 + 1) <= N - 1, right = 2 * c0 >= N - 1;
+            bool done = false;
+            if (full && c0 + 1 < N && (top || bottom) && (left || right)) {
+              float rowmax[kTileRows], colmax[2] = {0.f, 0.f};
 #pragma unroll
-            for (int i = 0; i < kTileRows; ++i) {
-              const int r = r0 + i;
-              if (r >= rend) break;
-              const int db = min(r, N - 1 - r);
+              for (int i = 0; i < kTileRows; ++i) {
+                rowmax[i] = fmaxf(acc[i][0], acc[i][1]);
+                colmax[0] = fmaxf(colmax[0], acc[i][0]);
+                colmax[1] = fmaxf(colmax[1], acc[i][1]);
+              }
+              const int dc_[2] = {left ? c0 : N - 1 - c0, left ? c0 + 1 : N - 2 - c0};
+              auto nearest = [&](float level, bool strict) -> int {
+                int d = 0x7fffffff;
 #pragma unroll
-              for (int j = 0; j < 2; ++j) {
-                const int c = c0 + j;
-                const int d = min(db, min(c, N - 1 - c));
-                if (c < N && d < my_margin && acc[i][j] > thr - delta) {
-                  if (acc[i][j] >= thr + delta) {
-                    my_margin = d;  // definitely above
-                  } else {
-                    // within float32 noise of the threshold: float64 decides, later and only
-                    // if it can still lower the margin
-                    const int slot = atomicAdd(&sm.ncand, 1);
-                    if (slot < kMaxCand) sm.cand[slot] = (r << 16) | c;
-                    else if (eval64(P, slots, r, c) > kEdgeThr) my_margin = d;
+                for (int i = 0; i < kTileRows; ++i) {
+                  const bool on = strict ? rowmax[i] > level : rowmax[i] >= level;
+                  const int db = top ? r0 + i : N - 1 - (r0 + i);
+                  if (on) d = min(d, db);
+                }
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                  const bool on = strict ? colmax[j] > level : colmax[j] >= level;
+                  if (on) d = min(d, dc_[j]);
+                }
+                return d;
+              };
+              const int d_lo = nearest(tl, true);
+              if (d_lo >= my_margin) {
+                done = true;  // nothing here can lower the margin
+              } else if (nearest(th, false) == d_lo) {
+                my_margin = d_lo;  // reached by a pixel definitely above the threshold
+                done = true;
+              }
+            }
+            if (!done) {
+#pragma unroll
+              for (int i = 0; i < kTileRows; ++i) {
+                const int r = r0 + i;
+                if (r >= rend) break;
+                const int db = min(r, N - 1 - r);
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                  const int c = c0 + j;
+                  const int dd = min(db, min(c, N - 1 - c));
+                  if (c < N && dd < my_margin && acc[i][j] > tl) {
+                    if (acc[i][j] >= th) {
+                      my_margin = dd;  // definitely above
+                    } else {
+                      // within float32 noise of the threshold: float64 decides, later and only
+                      // if it can still lower the margin
+                      const int slot = atomicAdd(&sm.ncand, 1);
+                      if (slot < kMaxCand) sm.cand[slot] = (r << 16) | c;
+                      else if (eval64(P, slots, r, c) > kEdgeThr) my_margin = dd;
+                    }
                   }
                 }
               }
@@ -651,7 +853,19 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           best_v = __uint_as_float((unsigned)(my_best >> 32));
         }
       }
+      DBG_LAP(dbg_epi);
+      rc = nx;
     }
+#ifdef RSB_TIMELINE
+    if (g_timeline && tid == 64) {
+      long long* tlp = &g_timeline[((size_t)img * 2 + rank) * 96 + 16];
+      tlp[1] = dbg_hit; tlp[2] = dbg_epi; tlp[3] = dbg_ntile; tlp[4] = dbg_nhit;
+    }
+    if (g_timeline && lane == 0) {
+      long long* tlp = &g_timeline[((size_t)img * 2 + rank) * 96 + 32 + warp * 4];
+      tlp[0] = clock64(); tlp[1] = dbg_ntile; tlp[2] = dbg_nhit; tlp[3] = dbg_start;
+    }
+#endif
 
     RSB_STAMP(1);  // this warp is out of tiles
     int margin = 0;
@@ -671,7 +885,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         image_best = theirs > image_best ? theirs : image_best;
       }
       RSB_STAMP(2);
-      if (tid == 0) sm.next_tile = 0;
       const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
       for (int e = tid; e < H * q4; e += kWorkers) {
@@ -712,7 +925,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       RSB_STAMP(2);
       if (margin >= N) margin = 0;  // empty mask -> idx 0 (argmax of an all-false array)
       if (tid == 0) {
-        sm.next_tile = 0;
         sm.next_row = 0;
         sm.foot_lo = N;
         sm.foot_hi = -1;
@@ -817,7 +1029,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         }
       }
 #ifdef RSB_TIMELINE
-      if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 16 + 11] = dbg_rows_out;
+      if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 96 + 11] = dbg_rows_out;
 #endif
       RSB_STAMP(4);
       worker_sync();  // (F) T complete in this band
@@ -964,11 +1176,12 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
 static size_t v2_bytes(int size, int cluster) {
   const int npad = (size + 3) & ~3;
   const int rows = size / cluster + (cluster > 1 ? 1 : 0);
-  return sizeof(v2::Fixed2) + (size_t)npad * 16 + (size_t)rows * npad * 4;
+  return sizeof(v2::Fixed2) + (size_t)npad * 96 + (size_t)rows * npad * 4;
 }
 
-bool v2_supported(int size, int* cluster, size_t* smem_bytes) {
+bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes) {
   int dev = 0, max_optin = 0;
+  if (slots > 32) return false;  // per-tile slot sets are 32-bit masks
   if (cudaGetDevice(&dev) != cudaSuccess) return false;
   if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess)
     return false;

@@ -147,7 +147,7 @@ __device__ inline void build_coefs(SM& sm, const double* P, int slots, int N, in
 
 
 // host-side launchers of the on-chip path (jet2.cu)
-bool v2_supported(int size, int* cluster, size_t* smem_bytes);
+bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes);
 int v2_launch(const Args& a, int cluster, size_t smem_bytes, cudaStream_t st);
 
 }  // namespace jet

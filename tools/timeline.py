@@ -10,14 +10,14 @@ np.random.seed(1)
 b = pack_jets(n, size, (3, 10), "normalize")
 d_p, d_z = L.dev_from(b.params), L.dev_from(b.zoom_pad)
 d_img = L.DeviceBuffer(n * size * size * 4); d_m = L.DeviceBuffer(n * 4); d_k = L.DeviceBuffer(n * 8)
-tl = L.DeviceBuffer(n * 2 * 16 * 8)
+tl = L.DeviceBuffer(n * 2 * 96 * 8)
 L.check(lib.rsb_memset(tl.ptr, 0, tl.nbytes, None))
 lib.rsb_debug_set_timeline.argtypes = [C.c_void_p]
 for rep in range(2):
     L.check(lib.rsb_debug_set_timeline(tl.ptr))
     L.check(lib.rsb_jet_render(d_p.ptr, d_z.ptr, n, 19, size, 1, d_img.ptr, d_m.ptr, d_k.ptr, None, 0, None))
     L.device_sync()
-t = tl.download((n, 2, 16), np.int64)
+t = tl.download((n, 2, 96), np.int64)
 zoom = b.zoom_pad >= 0
 names = ["A->tiles done (this warp)", "->C (cluster sync / exch)", "->table built", "->H pass done (warp)", "->F barrier", "->halo", "->V pass done", "->best exch", "->stores done"]
 for label, sel in [("zoom", zoom), ("plain", ~zoom)]:
@@ -43,3 +43,18 @@ gaps = []
 for i in range(n - ncl):
     gaps.append(t[i + ncl, 0, 0] - t[i, 0, 9])
 print("gap stamp9 -> next stamp0 (barrier A wait etc):", np.mean(gaps))
+print("phase 1: slot-tile hits per CTA: zoom", t[zoom][:,:,14].mean(), "plain", t[~zoom][:,:,14].mean(), " tiles computed per CTA: zoom", t[zoom][:,:,15].mean(), "plain", t[~zoom][:,:,15].mean())
+print("live slots: ", "see packer")
+for label, sel in [("zoom", zoom), ("plain", ~zoom)]:
+    tt = t[sel].astype(float)
+    print(label, "warp2: fetch+cull", tt[:,:,16].mean(), "hit loop", tt[:,:,17].mean(), "epilogue", tt[:,:,18].mean(), "tiles", tt[:,:,19].mean(), "hits", tt[:,:,20].mean(), "| stores", tt[:,:,21].mean(), "shfl-wait", tt[:,:,22].mean(), "order-lds+skip", tt[:,:,23].mean())
+tz = t[zoom].astype(float)
+w = tz[:, :, 32:96].reshape(len(tz), 2, 16, 4)
+s0 = tz[:, :, 0][:, :, None]
+print("zoom per warp: start-after-A / finish-after-A / tiles / hits")
+for k in range(16):
+    print(f"  warp {k:2d}: start {np.mean(w[:,:,k,3]-s0[:,:,0]):8.0f} finish {np.mean(w[:,:,k,0]-s0[:,:,0]):8.0f} tiles {w[:,:,k,1].mean():5.2f} hits {w[:,:,k,2].mean():6.2f}")
+print("  last finisher mean:", np.mean(np.max(w[:,:,:,0]-s0, axis=2)), " first finisher mean:", np.mean(np.min(w[:,:,:,0]-s0, axis=2)))
+bt = t[:, :, 24:29].astype(float)
+okb = bt[:, :, 4] > 0
+print("builder sections (slots / spans / dlo / lists):", [float(np.mean((bt[:,:,k+1]-bt[:,:,k])[okb])) for k in range(4)])
