@@ -77,7 +77,7 @@ struct __align__(16) Fixed2 {
   double params[3][kMaxSlots * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
   Coef2 coef[2][kMaxSlots];                            // double buffered, built one image ahead
   int hist[32];                     // build_coefs2 scratch: tiles per cost
-  double pix64[20 * kMaxSlots];     // peak64 scratch: 16 pixel x slot terms + 4 per-slot rotations
+  double pix64[22 * kMaxSlots + 8]; // peak64 scratch: 16 pixel x slot terms, 6 per-slot constants, tap coordinates
   uint64_t bar[3];
   unsigned long long xval[3][2];    // peer's margin / (unused) / arg-max key, [kind][use parity]
   uint64_t xbar[3];                 // mbarriers the peer's st.async completes: margin, halo, best
@@ -388,46 +388,67 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
 
 // ---- float64 peak (jet_max) for the labels, one warp -------------------------------
 // The float32 image fixes WHERE the maximum is; its float64 value is recomputed from the
-// parameters: <= 4x4 raw pixels x slots (operation order of gauss.py:77-88), combined with
-// float64 tap weights.  scratch: >= 16*slots + 4*slots doubles.
+// parameters: the raw pixels under the non-zero taps (<= 3 x 3) x slots, operation order of
+// gauss.py:77-88 except that the two divisions by sigma are multiplications by per-slot
+// reciprocals (a last-bit difference in the exponent's argument), combined with float64 tap
+// weights.  scratch: >= 16*slots + 6*slots + 8 doubles.
 __device__ inline double peak64(double* scratch, const double* P, int slots, int N, bool zoom,
                                 int zpad, int margin, unsigned long long image_best, int lane) {
   const unsigned idx = ~(unsigned)(image_best & 0xffffffffull);
   const int pr = (int)(idx / (unsigned)N), pc = (int)(idx % (unsigned)N);
-  double* rot = scratch + 16 * slots;  // per slot: cr, sr, ra, rb
+  double* rot = scratch + 16 * slots;      // per slot: cr, sr, ra, rb, 1/sy, 1/sx
+  int* coord = reinterpret_cast<int*>(rot + 6 * slots);  // [0..3] rows, [4..7] columns of the non-zero taps
   for (int k = lane; k < slots; k += 32) {
     const double* p = P + 6 * k;
-    const double cr = cos(p[5]), sr = sin(p[5]);
-    rot[4 * k] = cr;
-    rot[4 * k + 1] = sr;
-    rot[4 * k + 2] = p[2] * cr - p[1] * sr;
-    rot[4 * k + 3] = p[2] * sr + p[1] * cr;
+    double cr, sr;
+    sincos(p[5], &sr, &cr);
+    rot[6 * k] = cr;
+    rot[6 * k + 1] = sr;
+    rot[6 * k + 2] = p[2] * cr - p[1] * sr;
+    rot[6 * k + 3] = p[2] * sr + p[1] * cr;
+    rot[6 * k + 4] = 1.0 / p[4];
+    rot[6 * k + 5] = 1.0 / p[3];
   }
-  __syncwarp();
-  Taps64 tr, tc;
-  int npx = 1;
+  // taps with a non-zero weight, compacted: rows in even lanes' registers, columns in odd ones
+  // (both halves of the warp work at the same time)
+  Taps64 t;
   if (zoom) {
-    tr = composite_taps(pr, N, margin, zpad);
-    tc = composite_taps(pc, N, margin, zpad);
-    npx = 16;
+    t = composite_taps((lane & 1) ? pc : pr, N, margin, zpad);
   } else {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      tr.i[k] = pr; tc.i[k] = pc;
-      tr.w[k] = tc.w[k] = (k == 0) ? 1.0 : 0.0;
+      t.i[k] = (lane & 1) ? pc : pr;
+      t.w[k] = (k == 0) ? 1.0 : 0.0;
     }
   }
+  double w[4] = {0.0, 0.0, 0.0, 0.0};
+  int n = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (t.w[k] != 0.0) {
+      // (n <= k: a chain of selects instead of a dynamically indexed register array)
+#pragma unroll
+      for (int m = 0; m < 4; ++m)
+        if (m == n) w[m] = t.w[k];
+      if (lane < 2) coord[4 * lane + n] = t.i[k];
+      ++n;
+    }
+  }
+  const int nr = __shfl_sync(0xffffffffu, n, 0), nc = __shfl_sync(0xffffffffu, n, 1);
+  __syncwarp();
+  const int npx = nr * nc;
+  const unsigned inv_slots = (65536u + (unsigned)slots - 1u) / (unsigned)slots;  // exact below 1024
   for (int e = lane; e < npx * slots; e += 32) {
-    const int px = e / slots, k = e - px * slots;
-    const int i = px >> 2, j = px & 3;
+    const int px = (int)(((unsigned)e * inv_slots) >> 16), k = e - px * slots;
+    const int a = (px >= nc) + (px >= 2 * nc) + (px >= 3 * nc), b = px - a * nc;
     const double* p = P + 6 * k;
     double v = 0.0;
-    if (p[0] != 0.0 && tr.w[i] * tc.w[j] != 0.0) {
-      const int r = tr.i[i], c = tc.i[j];
-      const double cr = rot[4 * k], sr = rot[4 * k + 1];
-      const double ua = r * cr - c * sr, ub = r * sr + c * cr;
-      const double a = (rot[4 * k + 2] - ua) / p[4], b = (rot[4 * k + 3] - ub) / p[3];
-      v = p[0] * exp(-(a * a + b * b) / 2.0);
+    if (p[0] != 0.0) {
+      const int r = coord[a], c = coord[4 + b];
+      const double* ro = rot + 6 * k;
+      const double ua = r * ro[0] - c * ro[1], ub = r * ro[1] + c * ro[0];
+      const double ea = (ro[2] - ua) * ro[4], eb = (ro[3] - ub) * ro[5];
+      v = p[0] * exp(-(ea * ea + eb * eb) / 2.0);
     }
     scratch[e] = v;
   }
@@ -435,13 +456,19 @@ __device__ inline double peak64(double* scratch, const double* P, int slots, int
   double s = 0.0;
   if (lane < npx)
     for (int k = 0; k < slots; ++k) s += scratch[lane * slots + k];  // slot order
+  // rows' weights live in lane 0, columns' in lane 1
   double acc = 0.0;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int a = 0; a < 4; ++a) {
     double h = 0.0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) h += tc.w[j] * __shfl_sync(0xffffffffu, s, (i * 4 + j) & (npx - 1));
-    acc += tr.w[i] * h;
+    for (int b = 0; b < 4; ++b) {
+      const double wc = __shfl_sync(0xffffffffu, w[b], 1);
+      const double sv = __shfl_sync(0xffffffffu, s, (a * nc + b) & 31);
+      if (a < nr && b < nc) h += wc * sv;
+    }
+    const double wr = __shfl_sync(0xffffffffu, w[a], 0);
+    if (a < nr) acc += wr * h;
   }
   __syncwarp();
   return acc;
@@ -630,7 +657,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     // a shared-memory round trip queues behind the other warps' MUFU work.
     int my_margin = N;
     unsigned long long my_best = 0ull;
-    float best_v = -1.f;
+    float best_v = -1.f;  // this lane's running maximum and its pixel index
+    int best_i = 0;
 #ifdef RSB_TIMELINE
     long long dbg_t0 = clock64(), dbg_hit = 0, dbg_epi = 0, dbg_ntile = 0, dbg_nhit = 0;
     const long long dbg_start = dbg_t0;
@@ -750,6 +778,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
       for (int i = 0; i < kTileRows; ++i) f2_unpack(acc2[i], acc[i][0], acc[i][1]);
       DBG_LAP(dbg_hit);
+      if (c0 + 1 >= N) {  // odd size: the pair's second column lies outside the image
+#pragma unroll
+        for (int i = 0; i < kTileRows; ++i) acc[i][1] = 0.f;
+      }
       if (c0 < N) {
         float tile_top = 0.f;
         const bool full = r0 + kTileRows <= rend;  // always, when the band is a multiple of 8 rows
@@ -838,19 +870,20 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
             }
           }
         } else if (normalize && tile_top >= best_v) {
+          // first pixel (smallest index) that holds the tile's maximum; tiles come in no
+          // particular order, so equal values are decided by the index
+          int pi = 0x7fffffff;
 #pragma unroll
-          for (int i = 0; i < kTileRows; ++i) {
-            const int r = r0 + i;
-            if (r >= rend) break;
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-              if (c0 + j < N) {
-                const unsigned long long key = best_key(acc[i][j], r * N + c0 + j);
-                my_best = key > my_best ? key : my_best;
-              }
+          for (int i = kTileRows - 1; i >= 0; --i) {
+            if (r0 + i < rend) {
+              if (acc[i][1] == tile_top) pi = (r0 + i) * N + c0 + 1;
+              if (acc[i][0] == tile_top) pi = (r0 + i) * N + c0;
             }
           }
-          best_v = __uint_as_float((unsigned)(my_best >> 32));
+          if (tile_top > best_v || pi < best_i) {
+            best_v = tile_top;
+            best_i = pi;
+          }
         }
       }
       DBG_LAP(dbg_epi);
@@ -875,7 +908,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     if (!zoom) {
       // ------------- plain branch ---------------------------------------------------
       if (normalize) {
-        my_best = warp_max_u64(my_best);
+        my_best = warp_max_u64(best_v >= 0.f ? best_key(best_v, best_i) : 0ull);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
       }
       worker_sync();
@@ -1050,8 +1083,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       // V pass: results stay in registers (<= 8 rows x NS strips of 4 columns per lane)
       const int vr0 = max(R0, flo), vr1 = min(R0 + H - 1, fhi);  // inclusive footprint rows
       float4 res[kRowsPerWarp][NS];
-      my_best = 0ull;
+      // running maximum of this lane: value and pixel index (its pixels come in increasing
+      // index order, so '>' keeps the first of equal values)
       best_v = -1.f;
+      best_i = 0;
 #pragma unroll
       for (int i = 0; i < kRowsPerWarp; ++i) {
         const int r = R0 + warp + i * kWarps;
@@ -1080,17 +1115,16 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           }
           res[i][s] = v;
           if (normalize) {
-            const float top = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
-            if (top >= best_v) {
-              const float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                if (c0 + j < N) {
-                  const unsigned long long key = best_key(vv[j], r * N + c0 + j);
-                  my_best = key > my_best ? key : my_best;
-                }
-              }
-              best_v = __uint_as_float((unsigned)(my_best >> 32));
+            float4 m = v;
+            if (c0 + 3 >= N) {  // ragged last group: columns >= N do not take part
+              if (c0 + 1 >= N) m.y = -1.f;
+              if (c0 + 2 >= N) m.z = -1.f;
+              m.w = -1.f;
+            }
+            const float top = fmaxf(fmaxf(m.x, m.y), fmaxf(m.z, m.w));
+            if (top > best_v) {
+              best_v = top;
+              best_i = r * N + c0 + (m.x == top ? 0 : (m.y == top ? 1 : (m.z == top ? 2 : 3)));
             }
           }
         }
@@ -1098,7 +1132,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       RSB_STAMP(7);
       float inv = 1.f;
       if (normalize) {
-        my_best = warp_max_u64(my_best);
+        my_best = warp_max_u64(best_v >= 0.f ? best_key(best_v, best_i) : 0ull);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
         worker_sync();  // (G) this band's arg-max complete
         image_best = sm.lbest;

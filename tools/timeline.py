@@ -58,3 +58,6 @@ print("  last finisher mean:", np.mean(np.max(w[:,:,:,0]-s0, axis=2)), " first f
 bt = t[:, :, 24:29].astype(float)
 okb = bt[:, :, 4] > 0
 print("builder sections (slots / spans / dlo / lists):", [float(np.mean((bt[:,:,k+1]-bt[:,:,k])[okb])) for k in range(4)])
+print("hits per CTA by rank (zoom):", w[:, 0, :, 2].sum(axis=1).mean(), w[:, 1, :, 2].sum(axis=1).mean(), " tiles:", w[:, 0, :, 1].sum(axis=1).mean(), w[:, 1, :, 1].sum(axis=1).mean())
+fin = w[:, :, 2:, 0] - s0
+print("worker finish by rank (zoom): mean", fin[:, 0].mean(), fin[:, 1].mean(), " max", fin[:, 0].max(axis=1).mean(), fin[:, 1].max(axis=1).mean())
