@@ -145,6 +145,9 @@ __device__ __forceinline__ void sts_f32(uint32_t a, float v) {
 __device__ __forceinline__ void sts_v2(uint32_t a, float x, float y) {
   asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
 }
+__device__ __forceinline__ void sts_b64(uint32_t a, unsigned long long v) {
+  asm volatile("st.shared.b64 [%0], %1;" ::"r"(a), "l"(v) : "memory");
+}
 __device__ __forceinline__ void sts_v4(uint32_t a, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }

@@ -177,7 +177,8 @@ __device__ __forceinline__ int round_fma(float x) {
 #define RSB_BSTAMP(k) do {} while (0)
 #endif
 __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
-                                    int H, int lane, bool zoom, long long* dbg_tl = nullptr) {
+                                    int H, int lane, bool zoom, int first_worker,
+                                    long long* dbg_tl = nullptr) {
   RSB_BSTAMP(0);
   SlotGeo* geo = reinterpret_cast<SlotGeo*>(sm.geo);
   float amax = 0.f;
@@ -274,8 +275,9 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
   // 32 frames are tried at once, one per lane (dlo only feeds the tile skip, a multiple of
   // `step` is as good as the exact value).
   int dlo = 0;
+  all_nonneg = __all_sync(0xffffffffu, all_nonneg);
   if (zoom) {
-    certified = __any_sync(0xffffffffu, certified) && __all_sync(0xffffffffu, all_nonneg);
+    certified = __any_sync(0xffffffffu, certified) && all_nonneg;
     // without the certificate an empty mask (margin := 0, whole image used) cannot be ruled out
     if (certified) {
       const int half = (N - 1) / 2, step = (half + 31) / 32;
@@ -299,7 +301,12 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
   }
   if (lane == 0) {
     sm.nlive[cb] = base;
-    sm.delta[cb] = 6e-6f * fmaxf(1.f, amax);
+    // float32 noise of a rendered pixel near the 0.01 threshold.  All amplitudes >= 0: every
+    // term's error is relative to the term (<= 3e-5: SFU 2^-22 per factor, argument rounding
+    // with cancellation, accumulation), so the sum's is relative to the pixel value; plus
+    // the tails dropped by the footprint cut (slots x tau).  Otherwise: relative to the
+    // largest amplitude.
+    sm.delta[cb] = all_nonneg ? 3e-7f + 4e-7f * amax : 6e-6f * fmaxf(1.f, amax);
     sm.dlo[cb] = dlo;
   }
   RSB_BSTAMP(3);
@@ -372,14 +379,15 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
       for (int h = 0; h < 2; ++h)
         if (c > cost[h]) above[h] += n;
     }
-    // Snake deal over the 14 warps without a side job.
-    constexpr int kSeats = kWarps - 2;
+    // Snake deal over the warps without a side job: first_worker .. kWarps - 1.
+    const int seats = kWarps - first_worker;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       if (cost[h] == 0) continue;
       const int i = above[h] + among[h];
-      const int ps = i / kSeats, j = i - ps * kSeats;
-      const int w = 2 + ((ps & 1) ? j : kSeats - 1 - j), e = ps;
+      const int ps = (i >= seats) + (i >= 2 * seats) + (i >= 3 * seats) + (i >= 4 * seats) + (i >= 5 * seats);
+      const int j = i - ps * seats;
+      const int w = first_worker + ((ps & 1) ? j : seats - 1 - j), e = ps;
       sm.rec[cb][w][e] = make_uint2(hits[h], (unsigned)tag[h]);
     }
   }
@@ -583,9 +591,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     prefetch(cid, 0);
     if (cid + nclusters < a.n) prefetch(cid + nclusters, 1);
   }
+  // warp 1 only has its side job (the labels) in the cluster's first CTA; elsewhere it renders
+  const int first_worker = (rank == 0) ? 2 : 1;
   if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
-    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0);
+    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker);
   }
   // the peer CTA is resident and its mbarriers are initialised before any st.async
   if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -627,10 +637,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
 #ifdef RSB_TIMELINE
           build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane, a.zoom_pad[img + nclusters] >= 0,
-                       g_timeline ? &g_timeline[((size_t)img * 2 + rank) * 96 + 24] : nullptr);
+                       first_worker, g_timeline ? &g_timeline[((size_t)img * 2 + rank) * 96 + 24] : nullptr);
 #else
           build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane,
-                       a.zoom_pad[img + nclusters] >= 0);
+                       a.zoom_pad[img + nclusters] >= 0, first_worker);
 #endif
         }
         RSB_STAMP_T(12, kCoefWarp * 32);
@@ -693,6 +703,17 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       dbg_ntile++;
       dbg_nhit += __popc(rc.x);
 #endif
+      if (rc.x == 0u) {
+        // no slot touches this tile: zeros (the resampling taps may still read them)
+        load_first(nx);
+        if (c0 < N) {
+#pragma unroll
+          for (int i = 0; i < kTileRows; ++i)
+            if (r0 + i < rend) sts_b64(s_dst + (uint32_t)i * pitch4, 0ull);
+        }
+        rc = nx;
+        continue;
+      }
       f2 acc2[kTileRows];  // two adjacent pixels per row, packed (FFMA2)
 #pragma unroll
       for (int i = 0; i < kTileRows; ++i) acc2[i] = 0ull;
@@ -774,28 +795,32 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         slot_math(qb, cb, kb);
       }
       load_first(nx);  // in flight during the epilogue
+      if (c0 + 1 >= N) {  // odd size: the pair's second column lies outside the image
+#pragma unroll
+        for (int i = 0; i < kTileRows; ++i) {
+          float lo_, hi_;
+          f2_unpack(acc2[i], lo_, hi_);
+          acc2[i] = f2_pack(lo_, 0.f);
+        }
+      }
       float acc[kTileRows][2];
 #pragma unroll
       for (int i = 0; i < kTileRows; ++i) f2_unpack(acc2[i], acc[i][0], acc[i][1]);
       DBG_LAP(dbg_hit);
-      if (c0 + 1 >= N) {  // odd size: the pair's second column lies outside the image
-#pragma unroll
-        for (int i = 0; i < kTileRows; ++i) acc[i][1] = 0.f;
-      }
       if (c0 < N) {
         float tile_top = 0.f;
         const bool full = r0 + kTileRows <= rend;  // always, when the band is a multiple of 8 rows
         if (full) {
 #pragma unroll
           for (int i = 0; i < kTileRows; ++i) {
-            sts_v2(s_dst + (uint32_t)i * pitch4, acc[i][0], acc[i][1]);
+            sts_b64(s_dst + (uint32_t)i * pitch4, acc2[i]);
             tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
           }
         } else {
 #pragma unroll
           for (int i = 0; i < kTileRows; ++i) {
             if (r0 + i < rend) {
-              sts_v2(s_dst + (uint32_t)i * pitch4, acc[i][0], acc[i][1]);
+              sts_b64(s_dst + (uint32_t)i * pitch4, acc2[i]);
               tile_top = fmaxf(tile_top, fmaxf(acc[i][0], acc[i][1]));
             }
           }
@@ -935,6 +960,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       worker_sync();
       {
         const int ncand = min(sm.ncand, kMaxCand);
+#ifdef RSB_TIMELINE
+        if (g_timeline && tid == 64) g_timeline[((size_t)img * 2 + rank) * 96 + 29] = sm.ncand;
+#endif
         if (ncand > 0) {  // CTA-uniform, rare
           const int mdef = sm.lmargin;
           worker_sync();
@@ -945,7 +973,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
               double s = 0.0;
               for (int k0 = 0; k0 < slots; k0 += 32) {
                 const double t = (k0 + lane < slots) ? gauss64(P + 6 * (k0 + lane), r, c) : 0.0;
-                for (int l = 0; l < 32; ++l) s += __shfl_sync(0xffffffffu, t, l);  // slot order
+                for (int l = 0; l < min(32, slots - k0); ++l) s += __shfl_sync(0xffffffffu, t, l);  // slot order
               }
               if (lane == 0 && s > kEdgeThr) atomicMin(&sm.lmargin, d);
             }

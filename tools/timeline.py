@@ -61,3 +61,17 @@ print("builder sections (slots / spans / dlo / lists):", [float(np.mean((bt[:,:,
 print("hits per CTA by rank (zoom):", w[:, 0, :, 2].sum(axis=1).mean(), w[:, 1, :, 2].sum(axis=1).mean(), " tiles:", w[:, 0, :, 1].sum(axis=1).mean(), w[:, 1, :, 1].sum(axis=1).mean())
 fin = w[:, :, 2:, 0] - s0
 print("worker finish by rank (zoom): mean", fin[:, 0].mean(), fin[:, 1].mean(), " max", fin[:, 0].max(axis=1).mean(), fin[:, 1].max(axis=1).mean())
+for rk in (0, 1):
+    fw = 2 if rk == 0 else 1
+    cost = w[:, rk, fw:, 1] + w[:, rk, fw:, 2]
+    tm = (w[:, rk, fw:, 0] - w[:, rk, fw:, 3])
+    print(f"rank {rk}: dealt cost max/mean {np.mean(cost.max(axis=1) / cost.mean(axis=1)):.3f}  time max/mean {np.mean(tm.max(axis=1) / tm.mean(axis=1)):.3f}  corr(cost,time) {np.corrcoef(cost.ravel(), tm.ravel())[0,1]:.3f}")
+    # least squares time ~ a*tiles + b*hits
+    A = np.stack([w[:, rk, fw:, 1].ravel(), w[:, rk, fw:, 2].ravel()], axis=1)
+    coef, *_ = np.linalg.lstsq(A, tm.ravel(), rcond=None)
+    print("   time ~ %.0f * tiles + %.0f * hits" % tuple(coef))
+nc = t[zoom][:, :, 29]
+print("borderline candidates per CTA (zoom): mean %.3f, fraction of CTAs with any %.3f, max %d" % (nc.mean(), (nc > 0).mean(), nc.max()))
+sel = (nc > 0)
+d12 = (t[zoom][:, :, 2] - t[zoom][:, :, 1]).astype(float)
+print("stamp 1->2 with candidates %.0f, without %.0f" % (d12[sel].mean() if sel.any() else 0, d12[~sel].mean()))
