@@ -73,11 +73,13 @@ struct __align__(16) Coef2 {
 };
 static_assert(sizeof(Coef2) == 64, "Coef2 layout");
 
+constexpr int kSlots2 = 32;  // the launcher keeps slots <= 32 on this path (per-tile slot sets are 32-bit masks)
+
 struct __align__(16) Fixed2 {
-  double params[3][kMaxSlots * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
-  Coef2 coef[2][kMaxSlots];                            // double buffered, built one image ahead
+  double params[3][kSlots2 * RSB_JET_PARAM_STRIDE];  // triple buffered (bulk async copies)
+  Coef2 coef[2][kSlots2];                              // double buffered, built one image ahead
   int hist[32];                     // build_coefs2 scratch: tiles per cost
-  double pix64[22 * kMaxSlots + 8]; // peak64 scratch: 16 pixel x slot terms, 6 per-slot constants, tap coordinates
+  double pix64[22 * kSlots2 + 8];   // peak64 scratch: 16 pixel x slot terms, 6 per-slot constants, tap coordinates
   uint64_t bar[3];
   unsigned long long xval[3][2];    // peer's margin / (unused) / arg-max key, [kind][use parity]
   uint64_t xbar[3];                 // mbarriers the peer's st.async completes: margin, halo, best
@@ -89,7 +91,7 @@ struct __align__(16) Fixed2 {
   float delta[2];
   int dlo[2];                       // no pixel closer than this to the border exceeds 0.01
   struct LabelReq { unsigned long long best; int img, pb, margin, zpad; } label[2];  // [image parity]
-  float geo[kMaxSlots * 16];        // build_coefs2 scratch (SlotGeo per live slot)
+  float geo[kSlots2 * 16];          // build_coefs2 scratch (SlotGeo per live slot)
   int ncand;                        // borderline pixels awaiting a float64 verdict
   int cand[kMaxCand];               // r << 16 | c
   uint2 rec[2][kWarps][kMaxRec];    // per-warp work lists: {slots that touch the tile, row group << 8 | column tile}
@@ -565,9 +567,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
   const size_t esz = f64 ? 8 : 4;
-  // float32 output with contiguous rows: the finished band is staged in shared memory (over
-  // the raw image) and leaves through one bulk async copy
-  const bool bulk = false && !f64 && vec && pitch == N;  // measured: TMA drains shared memory no faster than STG (~30 B/clk/SM)
+  // float32 output with contiguous rows: the first stage_rows rows of the finished band are
+  // staged in shared memory and leave through one bulk async copy that drains while the next
+  // image is being rendered (an SM pushes ~30 B/clk towards L2 whichever engine stores, so
+  // the gain is the overlap, not the engine); the other rows are stored directly.
+  const int stage_rows = (!f64 && vec && pitch == N) ? a.stage_rows : 0;
+  float* stage = raw + (size_t)(H + (kCluster > 1 ? 1 : 0)) * pitch;
+  const uint32_t s_stage = keep_u32(smem_u32(stage));
+  const char* bulk_dst = nullptr;  // (thread 0) where the staged rows of the previous image go
 
   if (tid == 0) {
     mbar_init(&sm.bar[0], 1);
@@ -622,8 +629,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const int buf = it & 1;   // coefficient / exchange-slot parity
     const int pb = it % 3;    // parameter buffer
     mbar_wait(&sm.bar[pb], (it / 3) & 1);
-    if (tid == 0) bulk_wait_read();  // the previous image's band has left shared memory
-    __syncthreads();  // (A) coef/span/nlive of this image visible; raw free for reuse
+    __syncthreads();  // (A) coef/span/nlive of this image visible; raw free for reuse; stage complete
+    if (tid == 0 && bulk_dst) {
+      bulk_s2g(const_cast<char*>(bulk_dst), stage, (uint32_t)(stage_rows * N * 4));
+      bulk_dst = nullptr;
+    }
     if (tid == 0) {  // running reductions of this image (all reads of the previous values are behind A)
       sm.lbest = 0ull;
       sm.lmargin = N;
@@ -936,6 +946,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         my_best = warp_max_u64(best_v >= 0.f ? best_key(best_v, best_i) : 0ull);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
       }
+      if (tid == 0) bulk_wait_read();  // the previous image's staged rows have left the stage
       worker_sync();
       image_best = sm.lbest;
       if (normalize) {
@@ -945,13 +956,25 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       RSB_STAMP(2);
       const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
-      for (int e = tid; e < H * q4; e += kWorkers) {
-        const int rl = e / q4, c0 = (e - rl * q4) << 2;
-        const int r = R0 + rl;
-        float4 v = lds_v4(s_raw + (uint32_t)((r - base) * pitch + c0) * 4u);
-        v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-        if (bulk) *reinterpret_cast<float4*>(raw + (size_t)(r - base) * pitch + c0) = v;
-        else store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+      if (!f64 && vec && pitch == N) {
+        // float32, 16-byte aligned contiguous rows: the band is one run of float4
+        const uint32_t s_src = s_raw + (uint32_t)((R0 - base) * pitch) * 4u;
+        float4* outv = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + (size_t)R0 * N);
+        const int nstage = stage_rows * q4;
+        for (int e = tid; e < H * q4; e += kWorkers) {
+          float4 v = lds_v4(s_src + (uint32_t)e * 16u);
+          v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+          if (e < nstage) sts_v4(s_stage + (uint32_t)e * 16u, v);
+          else outv[e] = v;
+        }
+      } else {
+        for (int e = tid; e < H * q4; e += kWorkers) {
+          const int rl = e / q4, c0 = (e - rl * q4) << 2;
+          const int r = R0 + rl;
+          float4 v = lds_v4(s_raw + (uint32_t)((r - base) * pitch + c0) * 4u);
+          v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+          store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+        }
       }
     } else {
       // ------------- zoom branch ------------------------------------------------------
@@ -1159,6 +1182,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       }
       RSB_STAMP(7);
       float inv = 1.f;
+      if (tid == 0) bulk_wait_read();  // the previous image's staged rows have left the stage
+      if (!normalize && stage_rows > 0) worker_sync();
       if (normalize) {
         my_best = warp_max_u64(best_v >= 0.f ? best_key(best_v, best_i) : 0ull);
         if (lane == 0) atomicMax(&sm.lbest, my_best);
@@ -1169,27 +1194,43 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         inv = 1.f / __uint_as_float((unsigned)(image_best >> 32));
       }
       RSB_STAMP(8);
-      if (bulk && !normalize) worker_sync();  // every V-pass read of raw is done
+      if (!f64 && vec) {
+        // float32, 16-byte aligned rows: the common case, kept free of the general store's
+        // branches (they cost more issue slots than the stores themselves)
+        float* outf = reinterpret_cast<float*>(out) + (size_t)(R0 + warp) * N + 4 * lane;
+        const uint32_t s_st = s_stage + (uint32_t)(warp * N + 4 * lane) * 4u;
 #pragma unroll
-      for (int i = 0; i < kRowsPerWarp; ++i) {
-        const int r = R0 + warp + i * kWarps;
-        if (r >= R0 + H) continue;
+        for (int i = 0; i < kRowsPerWarp; ++i) {
+          const int rl = warp + i * kWarps;
+          if (rl >= H) continue;
 #pragma unroll
-        for (int s = 0; s < NS; ++s) {
-          const int c0 = s * kStrip + 4 * lane;
-          if (s >= strips || c0 >= N) continue;
-          float4 v = res[i][s];
-          v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-          if (bulk) *reinterpret_cast<float4*>(raw + (size_t)(r - base) * pitch + c0) = v;
-          else store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+          for (int s = 0; s < NS; ++s) {
+            if (s >= strips || s * kStrip + 4 * lane >= N) continue;
+            float4 v = res[i][s];
+            v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+            if (rl < stage_rows) sts_v4(s_st + (uint32_t)(i * kWarps * N + s * kStrip) * 4u, v);
+            else *reinterpret_cast<float4*>(outf + (size_t)i * kWarps * N + s * kStrip) = v;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < kRowsPerWarp; ++i) {
+          const int rl = warp + i * kWarps, r = R0 + rl;
+          if (rl >= H) continue;
+#pragma unroll
+          for (int s = 0; s < NS; ++s) {
+            const int c0 = s * kStrip + 4 * lane;
+            if (s >= strips || c0 >= N) continue;
+            float4 v = res[i][s];
+            v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+            store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+          }
         }
       }
     }
-    if (bulk) {
-      fence_proxy_async();  // my shared-memory writes -> visible to the async (TMA) proxy
-      worker_sync();
-      if (tid == 0)
-        bulk_s2g(out + (size_t)R0 * N * 4, raw + (size_t)(R0 - base) * pitch, (uint32_t)(H * N * 4));
+    if (stage_rows > 0) {
+      fence_proxy_async();  // my writes to the stage -> visible to the async (TMA) proxy
+      bulk_dst = out + (size_t)R0 * N * 4;  // issued by thread 0 behind the next barrier
     }
 
     RSB_STAMP(9);
@@ -1200,8 +1241,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       sm.label[buf] = q;
     }
   }
-  if (tid == 0) bulk_wait_read();
   __syncthreads();
+  if (tid == 0 && bulk_dst) {
+    bulk_s2g(const_cast<char*>(bulk_dst), stage, (uint32_t)(stage_rows * N * 4));
+    bulk_wait_all();
+  }
   if (rank == 0 && warp == kLabelWarp && it > 0) label_job((it - 1) & 1);
   if constexpr (kCluster > 1) cg::this_cluster().sync();  // no CTA exits while its smem is in use
 }
@@ -1235,10 +1279,15 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
 
 }  // namespace v2
 
-static size_t v2_bytes(int size, int cluster) {
+static size_t v2_bytes(int size, int cluster, int stage_rows = 0) {
   const int npad = (size + 3) & ~3;
   const int rows = size / cluster + (cluster > 1 ? 1 : 0);
-  return sizeof(v2::Fixed2) + (size_t)npad * 96 + (size_t)rows * npad * 4;
+  return sizeof(v2::Fixed2) + (size_t)npad * 16 + (size_t)(rows + stage_rows) * npad * 4;
+}
+// rows of a band that are staged for the bulk store: half the band when that fits
+static int v2_stage_rows(int size, int cluster, int max_optin) {
+  const int half = (size / cluster) / 2;
+  return v2_bytes(size, cluster, half) <= (size_t)max_optin ? half : 0;
 }
 
 bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes) {
@@ -1249,18 +1298,23 @@ bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes) {
     return false;
   if (size <= v2::kMaxBand && v2_bytes(size, 1) <= (size_t)max_optin) {
     *cluster = 1;
-    *smem_bytes = v2_bytes(size, 1);
+    *smem_bytes = v2_bytes(size, 1, v2_stage_rows(size, 1, max_optin));
     return true;
   }
   if ((size & 1) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
     *cluster = 2;
-    *smem_bytes = v2_bytes(size, 2);
+    *smem_bytes = v2_bytes(size, 2, v2_stage_rows(size, 2, max_optin));
     return true;
   }
   return false;
 }
 
-int v2_launch(const Args& a, int cluster, size_t smem_bytes, cudaStream_t st) {
+int v2_launch(const Args& a_in, int cluster, size_t smem_bytes, cudaStream_t st) {
+  Args a = a_in;
+  a.stage_rows = (int)((smem_bytes - v2_bytes(a.size, cluster)) / ((size_t)((a.size + 3) & ~3) * 4));
+#ifdef RSB_TIMELINE
+  fprintf(stderr, "v2_launch: size %d cluster %d smem %zu fixed %zu stage_rows %d\n", a.size, cluster, smem_bytes, sizeof(v2::Fixed2), a.stage_rows);
+#endif
   const int strips = (a.size + kStrip - 1) / kStrip;  // <= 2 for size <= 256
   if (cluster == 1)
     return strips <= 1 ? v2::launch_v2<1, 1>(a, smem_bytes, st) : v2::launch_v2<1, 2>(a, smem_bytes, st);

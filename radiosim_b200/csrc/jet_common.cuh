@@ -30,6 +30,7 @@ struct Args {
   double* peak;
   float* scratch;  // per-CTA raw-image slots when the image does not fit in smem
   int pitch;       // floats per stored raw row (size rounded up to 4)
+  int stage_rows = 0;  // on-chip path: rows of each band that leave through a staged bulk copy
 };
 
 // ---- float64 evaluation of one raw pixel, operation order of gauss.py:77-88 ----
