@@ -90,6 +90,11 @@ __device__ __forceinline__ uint32_t keep_u32(uint32_t v) {
   asm volatile("mov.u32 %0, %0;" : "+r"(v));
   return v;
 }
+template <class T>
+__device__ __forceinline__ T* keep_ptr(T* p) {
+  asm volatile("mov.u64 %0, %0;" : "+l"(p));
+  return p;
+}
 __device__ __forceinline__ float keep_f32(float v) {
   asm volatile("mov.f32 %0, %0;" : "+f"(v));
   return v;

@@ -81,6 +81,7 @@ struct __align__(16) Fixed2 {
   int hist[32];                     // build_coefs2 scratch: tiles per cost
   double pix64[22 * kSlots2 + 8];   // peak64 scratch: 16 pixel x slot terms, 6 per-slot constants, tap coordinates
   uint64_t bar[3];
+  double scale[2];                  // composite operator: (N + 2 pad) / N and (N - 2 margin) / N of this image
   unsigned long long xval[3][2];    // peer's margin / (unused) / arg-max key, [kind][use parity]
   uint64_t xbar[3];                 // mbarriers the peer's st.async completes: margin, halo, best
   unsigned long long lbest;         // this CTA's running arg-max key
@@ -1012,8 +1013,13 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         sm.next_row = 0;
         sm.foot_lo = N;
         sm.foot_hi = -1;
+        // the two scale factors of the composite operator, once per image
+        sm.scale[0] = (double)(N + 2 * zpad) / (double)N;
+        sm.scale[1] = (double)(N - 2 * margin) / (double)N;
       }
-      worker_sync();  // foot_* initialised before the atomics below
+      worker_sync();  // foot_* initialised before the atomics below; scale[] visible
+      const double sP = sm.scale[0], sC = sm.scale[1];
+      RSB_STAMP(30);
 
       // composite tap table (float64 math, float32 weights) + output footprint
       {
@@ -1023,7 +1029,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           m.w[0] = m.w[1] = m.w[2] = 0.f;
           m.i = 0;
           if (d < N) {
-            m = merge_taps(composite_taps(d, N, margin, zpad), N);
+            m = merge_taps(composite_taps(d, N, margin, zpad, sP, sC), N);
             if (m.w[0] != 0.f || m.w[1] != 0.f || m.w[2] != 0.f) {
               lo = min(lo, d);
               hi = max(hi, d);
@@ -1033,6 +1039,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           for (int k = 0; k < 3; ++k) tab_w[k * npad + d] = m.w[k];
           tab_i[d] = m.i;
         }
+        RSB_STAMP(31);
         lo = warp_min(lo);
         hi = -warp_min(-hi);
         if (lane == 0) {
@@ -1197,20 +1204,26 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       if (!f64 && vec) {
         // float32, 16-byte aligned rows: the common case, kept free of the general store's
         // branches (they cost more issue slots than the stores themselves)
-        float* outf = reinterpret_cast<float*>(out) + (size_t)(R0 + warp) * N + 4 * lane;
-        const uint32_t s_st = s_stage + (uint32_t)(warp * N + 4 * lane) * 4u;
+        // (running addresses, laundered: the compiler otherwise rebuilds the 64-bit address
+        // from the kernel arguments in front of every store)
+        float* outf = keep_ptr(reinterpret_cast<float*>(out) + (size_t)(R0 + warp) * N + 4 * lane);
+        uint32_t s_st = keep_u32(s_stage + (uint32_t)(warp * N + 4 * lane) * 4u);
+        const uint32_t step = keep_u32((uint32_t)(kWarps * N));  // floats between this warp's rows
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
           const int rl = warp + i * kWarps;
-          if (rl >= H) continue;
+          if (rl < H) {
 #pragma unroll
-          for (int s = 0; s < NS; ++s) {
-            if (s >= strips || s * kStrip + 4 * lane >= N) continue;
-            float4 v = res[i][s];
-            v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-            if (rl < stage_rows) sts_v4(s_st + (uint32_t)(i * kWarps * N + s * kStrip) * 4u, v);
-            else *reinterpret_cast<float4*>(outf + (size_t)i * kWarps * N + s * kStrip) = v;
+            for (int s = 0; s < NS; ++s) {
+              if (s >= strips || s * kStrip + 4 * lane >= N) continue;
+              float4 v = res[i][s];
+              v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+              if (rl < stage_rows) sts_v4(s_st + (uint32_t)(s * kStrip) * 4u, v);
+              else *reinterpret_cast<float4*>(outf + s * kStrip) = v;
+            }
           }
+          outf += step;
+          s_st += step * 4u;
         }
       } else {
 #pragma unroll

@@ -59,11 +59,18 @@ struct Taps64 {
   int i[4];
   double w[4];
 };
+// sP = (double)(N + 2 pad) / (double)N and sC = (double)(N - 2 m) / (double)N are the same
+// for every coordinate of an image: callers that build whole tables pass them in (two float64
+// divisions less per entry; the FP64 pipe is narrow).
+__device__ inline Taps64 composite_taps(int d, int N, int m, int pad, double sP, double sC);
 __device__ inline Taps64 composite_taps(int d, int N, int m, int pad) {
+  return composite_taps(d, N, m, pad, (double)(N + 2 * pad) / (double)N, (double)(N - 2 * m) / (double)N);
+}
+__device__ inline Taps64 composite_taps(int d, int N, int m, int pad, double sP, double sC) {
   Taps64 t;
   const int P = N + 2 * pad;
   const int Cs = N - 2 * m;
-  double f = (d + 0.5) * ((double)P / (double)N) - 0.5;
+  double f = (d + 0.5) * sP - 0.5;
   int s = (int)floor(f);
   double w = f - (double)s;
   if (s < 0) { s = 0; w = 0.0; }
@@ -78,7 +85,7 @@ __device__ inline Taps64 composite_taps(int d, int N, int m, int pad) {
       t.w[2 * a] = t.w[2 * a + 1] = 0.0;
       continue;
     }
-    double g = (z[a] + 0.5) * ((double)Cs / (double)N) - 0.5;
+    double g = (z[a] + 0.5) * sC - 0.5;
     int u = (int)floor(g);
     double v = g - (double)u;
     if (u < 0) { u = 0; v = 0.0; }

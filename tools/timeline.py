@@ -75,3 +75,5 @@ print("borderline candidates per CTA (zoom): mean %.3f, fraction of CTAs with an
 sel = (nc > 0)
 d12 = (t[zoom][:, :, 2] - t[zoom][:, :, 1]).astype(float)
 print("stamp 1->2 with candidates %.0f, without %.0f" % (d12[sel].mean() if sel.any() else 0, d12[~sel].mean()))
+tz3 = t[zoom].astype(float)
+print("table: 2->sync %.0f, sync->loop done %.0f, loop done->3 %.0f" % ((tz3[:,:,30]-tz3[:,:,2]).mean(), (tz3[:,:,31]-tz3[:,:,30]).mean(), (tz3[:,:,3]-tz3[:,:,31]).mean()))
