@@ -525,12 +525,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   Fixed2& sm = *reinterpret_cast<Fixed2*>(smem_raw);
   const int N = a.size, pitch = a.pitch, slots = a.slots;
   const int npad = (N + 3) & ~3;
-  float* tab_w = reinterpret_cast<float*>(smem_raw + sizeof(Fixed2));  // [3][npad] weights
-  int* tab_i = reinterpret_cast<int*>(tab_w + 3 * npad);               // [npad] first tap (absolute)
-  float* raw = reinterpret_cast<float*>(tab_i + npad);                 // [H (+1 halo)][pitch]
+  // composite taps, one record per output coordinate: {w0, w1, w2, first tap (absolute, as int bits)}
+  float4* tab = reinterpret_cast<float4*>(smem_raw + sizeof(Fixed2));  // [npad]
+  float* raw = reinterpret_cast<float*>(tab + npad);                   // [H (+1 halo)][pitch]
 
-  const uint32_t s_raw = keep_u32(smem_u32(raw)), s_tabw = keep_u32(smem_u32(tab_w)),
-                 s_tabi = keep_u32(smem_u32(tab_i));
+  const uint32_t s_raw = keep_u32(smem_u32(raw)), s_tab = keep_u32(smem_u32(tab));
   const int tid = keep_s32((int)threadIdx.x), lane = tid & 31, warp = tid >> 5;
   const int rank = keep_s32((kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0);
   const int cid = blockIdx.x / kCluster, nclusters = gridDim.x / kCluster;
@@ -1035,13 +1034,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
               hi = max(hi, d);
             }
           }
-#pragma unroll
-          for (int k = 0; k < 3; ++k) tab_w[k * npad + d] = m.w[k];
-          tab_i[d] = m.i;
+          tab[d] = make_float4(m.w[0], m.w[1], m.w[2], __int_as_float(m.i));
         }
         RSB_STAMP(31);
-        lo = warp_min(lo);
-        hi = -warp_min(-hi);
+        lo = __reduce_min_sync(0xffffffffu, lo);
+        hi = __reduce_max_sync(0xffffffffu, hi);
         if (lane == 0) {
           if (lo < N) atomicMin(&sm.foot_lo, lo);
           if (hi >= 0) atomicMax(&sm.foot_hi, hi);
@@ -1068,10 +1065,12 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           for (int j = 0; j < 4; ++j) {
             const int cj = sc0 + 32 * j + lane;
             const int c = min(cj, npad - 1);
-#pragma unroll
-            for (int k = 0; k < 3; ++k)
-              ct[s][j].w[k] = (act[s] && cj < N) ? tab_w[k * npad + c] : 0.f;
-            ct[s][j].i = act[s] ? tab_i[c] : max((N >> 1) - 1, 0);
+            const float4 tp = lds_v4(s_tab + (uint32_t)c * 16u);
+            const bool on = act[s] && cj < N;
+            ct[s][j].w[0] = on ? tp.x : 0.f;
+            ct[s][j].w[1] = on ? tp.y : 0.f;
+            ct[s][j].w[2] = on ? tp.z : 0.f;
+            ct[s][j].i = act[s] ? __float_as_int(tp.w) : max((N >> 1) - 1, 0);
           }
         }
         const int rlo = max(R0, margin), rhi = min(R0 + H, N - margin);
@@ -1151,10 +1150,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 #pragma unroll
         for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < vr0 || r > vr1) continue;  // warp-uniform
-        const float w0 = lds_f32(s_tabw + (uint32_t)r * 4u), w1 = lds_f32(s_tabw + (uint32_t)(npad + r) * 4u),
-                    w2 = lds_f32(s_tabw + (uint32_t)(2 * npad + r) * 4u);
+        const float4 tp = lds_v4(s_tab + (uint32_t)r * 16u);
+        const float w0 = tp.x, w1 = tp.y, w2 = tp.z;
         // only zero-weight taps can fall outside this band (+ halo): clamp them
-        const int l0 = lds_s32(s_tabi + (uint32_t)r * 4u) - base;
+        const int l0 = __float_as_int(tp.w) - base;
         const uint32_t p0 = s_raw + (uint32_t)(min(max(l0, 0), H) * pitch) * 4u;
         const uint32_t p1 = s_raw + (uint32_t)(min(max(l0 + 1, 0), H) * pitch) * 4u;
         const uint32_t p2 = s_raw + (uint32_t)(min(max(l0 + 2, 0), H) * pitch) * 4u;
