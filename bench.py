@@ -42,7 +42,7 @@ COMPS = (3, 10)
 SLOTS = 2 * COMPS[1] - 1
 METRIC = "images/sec (whole box) for 256x256 jet batches"
 UNIT = "images/s"
-NCU_DRAM_BYTES_PER_IMAGE = 250230  # measured, see profiles/README.md
+NCU_DRAM_BYTES_PER_IMAGE = 248657  # measured, see profiles/README.md
 WORKLOAD = "C5: jet 256x256, default jet params (num_jet_components [3,10], scaling normalize)"
 
 
@@ -328,7 +328,7 @@ def run_cuda(args):
                 "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved_gbs / hbm_peak,
                 # dram__bytes_read+write of one launch from the ncu --set full capture, scaled to
-                # this launch's batch (profiles/r01_jet2_kernel_ncu_full_raw.csv: 1.0249 GB / 4096 jets)
+                # this launch's batch (profiles/r01_jet2_kernel_ncu_full_raw.csv: 1.0185 GB / 4096 jets)
                 "traffic": NCU_DRAM_BYTES_PER_IMAGE * batch, "traffic_unit": "bytes per launch",
                 "traffic_source": "ncu --set full, 4096-jet launch, scaled by batch",
                 "peak_source": peak_src,
