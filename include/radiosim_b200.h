@@ -226,6 +226,25 @@ int rsb_jet_render_static(const double* params_dev, const int32_t* zoom_pad_dev,
                           int slots, int size, unsigned flags, void* out_img_dev,
                           int32_t* out_margin_dev, double* out_peak_dev, void* stream);
 
+/* ---- host-side parameter packer (no GPU involved) -------------------------------------
+ * Replaces the per-image RNG chain of create_jet, reference src/radiosim/jets/jet.py:54-125
+ * (component count, amplitudes, knots, widths, rotations, boosting, centre shift, counter
+ * jet) and the data-dependent draw at :149-168 (zoom_out factor iff the border maximum is
+ * below 0.01), draw for draw on numpy's LEGACY global stream.
+ *   mt_key[624], mt_pos, has_gauss, cached_gauss : the tuple of np.random.get_state(), updated
+ *     in place -- write it back with np.random.set_state() and the stream continues where the
+ *     reference's would;
+ *   params [n, 2*comp_hi-1, 6] f64 (amp, x, y, sx, sy, rot), extra [n, 2*comp_hi-1, 2] f64
+ *     (z_rotation, beta), zoom_pad [n] i32 (-1 or int64(pad_value), jet.py:169), zoom_out [n] f64
+ *     : host buffers, as rsb_jet_render_host takes them;
+ *   border_counts [3] or NULL: += images whose border test was decided by the upper bound, by
+ *     one exact pixel, by the full border evaluation.
+ * scaling="mojave" (a scipy beta draw per image) is not covered: callers keep the Python
+ * packer for it.  1 <= comp_lo <= comp_hi <= 32. */
+int rsb_jet_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
+                 int n, int size, int comp_lo, int comp_hi, double* params, double* extra,
+                 int32_t* zoom_pad, double* zoom_out, long long* border_counts);
+
 #ifdef __cplusplus
 }
 #endif

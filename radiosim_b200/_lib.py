@@ -71,6 +71,8 @@ _SIGS = {
     "rsb_source_margin": ([_vp, _i32, C.c_double, _vp, _vp], _i32),
     "rsb_resize_linear": ([_vp, _i32, _i32, _sz, _i32, _i32, _vp, _i32, _vp], _i32),
     "rsb_jet_render_host": ([_vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp], _i32),
+    "rsb_jet_pack": ([_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(C.c_double), _i32, _i32, _i32, _i32,
+                      _vp, _vp, _vp, _vp, _vp], _i32),
 }
 for _name, (_args, _res) in _SIGS.items():
     if hasattr(_lib, _name):

@@ -1,0 +1,285 @@
+// Native host-side parameter packer for jets: the reference's RNG chain
+// (src/radiosim/jets/jet.py:54-125,168) replayed draw for draw on numpy's *legacy* global
+// stream, in C++ instead of Python.  Host code only -- no kernel in this file.
+//
+// The legacy RandomState is MT19937 plus four derived distributions, restated here from
+// numpy's published algorithm (numpy/random/src/mt19937/mt19937.c, legacy-distributions.c,
+// distributions.c; numpy 2.x):
+//   random_sample : (a >> 5, b >> 6) -> (a * 2^26 + b) / 2^53            (two 32-bit outputs)
+//   uniform(l, h) : l + (h - l) * random_sample
+//   normal(m, s)  : m + s * legacy_gauss; legacy_gauss = polar Box-Muller that returns f*x2 and
+//                   caches f*x1 for the next call (has_gauss / gauss of the state tuple)
+//   randint(l, h) : l + masked rejection of one 32-bit output against (h - 1 - l)
+// The caller passes the state tuple of np.random.get_state() and writes the updated one back
+// with np.random.set_state(), so the stream continues exactly where the reference's would.
+//
+// Elementary functions are libm's; numpy's array loops may use SIMD variants that differ in the
+// last bit, so parameters agree with the Python packer to ~1 ulp (tests/test_packer.py), the
+// stream position and every branch exactly.
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace rsb {
+namespace pack {
+
+struct Legacy {
+  uint32_t* key;  // [624]
+  int pos;
+  int has_gauss;
+  double gauss;
+
+  void refill() {
+    constexpr int N = 624, M = 397;
+    constexpr uint32_t MATRIX_A = 0x9908b0dfu, UPPER = 0x80000000u, LOWER = 0x7fffffffu;
+    uint32_t y;
+    int i;
+    for (i = 0; i < N - M; i++) {
+      y = (key[i] & UPPER) | (key[i + 1] & LOWER);
+      key[i] = key[i + M] ^ (y >> 1) ^ (-(int32_t)(y & 1) & MATRIX_A);
+    }
+    for (; i < N - 1; i++) {
+      y = (key[i] & UPPER) | (key[i + 1] & LOWER);
+      key[i] = key[i + (M - N)] ^ (y >> 1) ^ (-(int32_t)(y & 1) & MATRIX_A);
+    }
+    y = (key[N - 1] & UPPER) | (key[0] & LOWER);
+    key[N - 1] = key[M - 1] ^ (y >> 1) ^ (-(int32_t)(y & 1) & MATRIX_A);
+    pos = 0;
+  }
+  uint32_t next32() {
+    if (pos == 624) refill();
+    uint32_t y = key[pos++];
+    y ^= (y >> 11);
+    y ^= (y << 7) & 0x9d2c5680u;
+    y ^= (y << 15) & 0xefc60000u;
+    y ^= (y >> 18);
+    return y;
+  }
+  double sample() {
+    const int32_t a = (int32_t)(next32() >> 5), b = (int32_t)(next32() >> 6);
+    return (a * 67108864.0 + b) / 9007199254740992.0;
+  }
+  double uniform(double low, double high) {
+    const double range = high - low;
+    return low + range * sample();
+  }
+  double legacy_gauss() {
+    if (has_gauss) {
+      const double t = gauss;
+      has_gauss = 0;
+      gauss = 0.0;
+      return t;
+    }
+    double f, x1, x2, r2;
+    do {
+      x1 = 2.0 * sample() - 1.0;
+      x2 = 2.0 * sample() - 1.0;
+      r2 = x1 * x1 + x2 * x2;
+    } while (r2 >= 1.0 || r2 == 0.0);
+    f = std::sqrt(-2.0 * std::log(r2) / r2);
+    gauss = f * x1;
+    has_gauss = 1;
+    return f * x2;
+  }
+  double normal(double loc, double scale) { return loc + scale * legacy_gauss(); }
+  // RandomState.randint(low, high) for a range below 2^32: masked rejection, one 32-bit output per try
+  int64_t randint(int64_t low, int64_t high) {
+    const uint64_t rng = (uint64_t)(high - 1 - low);
+    if (rng == 0) return low;
+    uint32_t mask = (uint32_t)rng;
+    mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+    uint32_t v;
+    do v = next32() & mask; while (v > (uint32_t)rng);
+    return low + (int64_t)v;
+  }
+};
+
+constexpr int kMaxHi = 32;  // components per side the arrays below are sized for
+
+// one slot's value at a border pixel, operation order of utils/gauss.py:77-88
+struct SlotRot {
+  double amp, cs, sn, ra, rb, wx, wy;
+};
+inline double slot_at(const SlotRot& s, double r, double c) {
+  const double ua = r * s.cs - c * s.sn, ub = r * s.sn + c * s.cs;
+  const double a = (s.ra - ua) / s.wy, b = (s.rb - ub) / s.wx;
+  return s.amp * std::exp(-(a * a + b * b) / 2.0);
+}
+
+// jet.py:149-157: is the maximum of the summed components over the 4(N-1) border pixels
+// below 0.01?  The reference evaluates every border pixel; here two rigorous shortcuts come
+// first and the full evaluation only runs when neither decides:
+//   (1) upper bound: a slot's maximum over a whole border LINE is amp * exp(-q/2) with q the
+//       smallest value of its quadratic form on that line; the sum of the slots' largest line
+//       values bounds every border pixel;
+//   (2) lower bound: the exact sum (reference operation order) at the border pixel nearest to
+//       where the strongest slot peaks on its best line.
+// counts[0..2]: images decided by (1), by (2), by the full evaluation.
+inline bool border_below(const SlotRot* s, int slots, int size, long long* counts) {
+  const double thr = 0.01, last = (double)(size - 1);
+  double upper = 0.0, best = -1.0;
+  double best_r = 0.0, best_c = 0.0;
+  bool bounded = true;
+  for (int k = 0; k < slots; ++k) {
+    if (s[k].amp == 0.0) continue;
+    const double iy = 1.0 / (s[k].wy * s[k].wy), ix = 1.0 / (s[k].wx * s[k].wx);
+    const double mrr = s[k].cs * s[k].cs * iy + s[k].sn * s[k].sn * ix;
+    const double mcc = s[k].sn * s[k].sn * iy + s[k].cs * s[k].cs * ix;
+    const double mrc = s[k].cs * s[k].sn * (ix - iy);
+    const double det = mrr * mcc - mrc * mrc;
+    // centre in (row, column): ra = cy cs - cx sn, rb = cy sn + cx cs  ->  cy, cx
+    const double cy = s[k].ra * s[k].cs + s[k].rb * s[k].sn, cx = s[k].rb * s[k].cs - s[k].ra * s[k].sn;
+    if (!(det > 0.0) || !std::isfinite(det) || !std::isfinite(cy) || !std::isfinite(cx)) {
+      bounded = false;
+      break;
+    }
+    double qmin = INFINITY, pr = 0.0, pc = 0.0;
+    const double rows[2] = {0.0, last};
+    for (int e = 0; e < 2; ++e) {  // lines r = 0, r = N-1: minimum over the column offset
+      const double dr = rows[e] - cy, q = dr * dr * det / mcc;
+      if (q < qmin) { qmin = q; pr = rows[e]; pc = cx - mrc * dr / mcc; }
+    }
+    for (int e = 0; e < 2; ++e) {  // lines c = 0, c = N-1
+      const double dc = rows[e] - cx, q = dc * dc * det / mrr;
+      if (q < qmin) { qmin = q; pc = rows[e]; pr = cy - mrc * dc / mrr; }
+    }
+    const double v = std::fabs(s[k].amp) * std::exp(-0.5 * qmin * 0.999999);
+    upper += v;
+    if (v > best) { best = v; best_r = pr; best_c = pc; }
+  }
+  if (bounded && upper * 1.000001 < 0.0099) {
+    counts[0]++;
+    return true;
+  }
+  auto pixel = [&](double r, double c) {
+    double sum = 0.0;
+    for (int k = 0; k < slots; ++k) sum += (s[k].amp == 0.0) ? 0.0 : slot_at(s[k], r, c);
+    return sum;
+  };
+  if (bounded && best >= 0.0) {
+    const double r = std::fmin(std::fmax(std::nearbyint(best_r), 0.0), last);
+    const double c = std::fmin(std::fmax(std::nearbyint(best_c), 0.0), last);
+    if (!(pixel(r, c) < thr)) {  // (a NaN sum makes the reference's `max < 0.01` false as well)
+      counts[1]++;
+      return false;
+    }
+  }
+  counts[2]++;
+  // np.max propagates NaN, and `nan < 0.01` is False
+  double m = -INFINITY;
+  bool nan = false;
+  for (int i = 0; i < size; ++i) {
+    const double d = (double)i;
+    const double v[4] = {pixel(0.0, d), pixel(last, d), pixel(d, 0.0), pixel(d, last)};
+    for (int j = 0; j < 4; ++j) {
+      if (v[j] != v[j]) nan = true;
+      if (v[j] > m) m = v[j];
+    }
+  }
+  return !nan && m < thr;
+}
+
+}  // namespace pack
+}  // namespace rsb
+
+extern "C" int rsb_jet_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
+                            int n, int size, int comp_lo, int comp_hi, double* params, double* extra,
+                            int32_t* zoom_pad, double* zoom_out, long long* border_counts) {
+  using namespace rsb::pack;
+  RSB_ARG(mt_key && mt_pos && has_gauss && cached_gauss, "rsb_jet_pack: NULL generator state");
+  RSB_ARG(params && extra && zoom_pad && zoom_out, "rsb_jet_pack: NULL output");
+  RSB_ARG(n >= 0 && size >= 2, "rsb_jet_pack: n must be >= 0 and size >= 2 (got %d, %d)", n, size);
+  RSB_ARG(comp_lo >= 1 && comp_lo <= comp_hi && comp_hi <= kMaxHi,
+          "rsb_jet_pack: components must satisfy 1 <= lo <= hi <= %d (got %d, %d)", kMaxHi, comp_lo, comp_hi);
+  RSB_ARG(*mt_pos >= 0 && *mt_pos <= 624, "rsb_jet_pack: generator position %d out of range", *mt_pos);
+  Legacy g{mt_key, *mt_pos, *has_gauss, *cached_gauss};
+  long long counts_local[3] = {0, 0, 0};
+  long long* counts = border_counts ? border_counts : counts_local;
+  const int hi = comp_hi, slots = 2 * hi - 1;
+  const double pi = 3.141592653589793, N = (double)size;
+  const int mid = size / 2;
+  for (int b = 0; b < n; ++b) {
+    double amp[kMaxHi] = {0}, x[kMaxHi] = {0}, y[kMaxHi] = {0}, sx[kMaxHi] = {0}, sy[kMaxHi] = {0},
+           rot[kMaxHi] = {0}, beta[kMaxHi] = {0};
+    const int k = (int)g.randint(comp_lo, (int64_t)hi + 1);
+    rot[0] = g.uniform(0.0, pi);
+    const double beta1 = g.uniform(0.0, 1.0);
+    if (hi > 1) beta[1] = beta1;
+    double bend = g.uniform(0.0, pi);
+    const double tilt = g.uniform(0.0, pi / 2);
+    const double sin_tilt = std::sin(tilt);
+    for (int i = 0; i < k; ++i) {
+      amp[i] = std::exp(-std::sqrt((double)i) * g.normal(1.3, 0.2));
+      if (i >= 1 && g.sample() < 0.1) amp[i] = 0.0;
+      if (i >= 2) beta[i] = beta[1] * std::exp(-std::sqrt((double)(i - 1)) * g.normal(0.5, 0.1));
+      bend += g.normal(0.0, pi / 24);
+      const double cb = std::cos(bend), sb = std::sin(bend);
+      const double acb = std::fabs(cb), asb = std::fabs(sb);
+      const double fill = acb < asb ? 1.0 / asb : (acb > asb ? 1.0 / acb : std::sqrt(2.0));
+      const double dist = (double)i / (double)(k - 1) * N / 2 * fill * sin_tilt * 0.7;
+      x[i] = dist * cb + mid;
+      y[i] = dist * sb + mid;
+      const double num = N / (double)k * fill * std::sqrt((double)(i + 1));
+      const double p0 = num / g.uniform(3.0, 8.0), p1 = num / g.uniform(3.0, 8.0);
+      if (p0 >= p1) { sx[i] = p0; sy[i] = p1; } else { sx[i] = p1; sy[i] = p0; }
+      if (i >= 1) rot[i] = rot[i - 1] + g.normal(0.0, pi / 18);
+    }
+    const double mu = std::cos(tilt);
+    const double off_x = g.uniform(-N / 20, N / 20), off_y = g.uniform(-N / 20, N / 20);
+    double* p = params + (size_t)b * slots * 6;
+    double* ex = extra + (size_t)b * slots * 2;
+    std::memset(p, 0, sizeof(double) * slots * 6);
+    std::memset(ex, 0, sizeof(double) * slots * 2);
+    double away[kMaxHi];
+    for (int i = 0; i < hi; ++i) {
+      const double lorentz = 1.0 / std::sqrt(1.0 - beta[i] * beta[i]);
+      const double toward = 1.0 / (lorentz * (1.0 - beta[i] * mu));
+      away[i] = 1.0 / (lorentz * (1.0 + beta[i] * mu));
+      p[i * 6 + 0] = amp[i] * toward;
+      p[i * 6 + 1] = x[i] + off_x;
+      p[i * 6 + 2] = y[i] + off_y;
+      p[i * 6 + 3] = sx[i];
+      p[i * 6 + 4] = sy[i];
+      p[i * 6 + 5] = rot[i];
+      ex[i * 2 + 1] = beta[i];
+    }
+    for (int s = 0; s < slots; ++s) ex[s * 2] = tilt;
+    if (g.sample() < 0.3) {  // counter jet: mirror slots 1.. through the image centre
+      for (int i = 1; i < hi; ++i) {
+        double* q = p + (size_t)(hi + i - 1) * 6;
+        q[0] = amp[i] * away[i];
+        q[1] = N - x[i] + off_x;
+        q[2] = N - y[i] + off_y;
+        q[3] = sx[i];
+        q[4] = sy[i];
+        q[5] = rot[i];
+        ex[(hi + i - 1) * 2 + 1] = beta[i];
+      }
+    }
+    SlotRot sr[2 * kMaxHi];
+    for (int s = 0; s < slots; ++s) {
+      const double* q = p + (size_t)s * 6;
+      sr[s].amp = q[0];
+      if (q[0] == 0.0) continue;
+      sr[s].cs = std::cos(q[5]);
+      sr[s].sn = std::sin(q[5]);
+      sr[s].ra = q[2] * sr[s].cs - q[1] * sr[s].sn;
+      sr[s].rb = q[2] * sr[s].sn + q[1] * sr[s].cs;
+      sr[s].wx = q[3];
+      sr[s].wy = q[4];
+    }
+    zoom_pad[b] = -1;
+    zoom_out[b] = 1.0;
+    if (border_below(sr, slots, size, counts)) {
+      const double zo = g.uniform(0.5, 1.0);
+      zoom_out[b] = zo;
+      zoom_pad[b] = (int32_t)(int64_t)((1.0 / zo - 1.0) * N / 2);
+    }
+  }
+  *mt_pos = g.pos;
+  *has_gauss = g.has_gauss;
+  *cached_gauss = g.gauss;
+  return 0;
+}

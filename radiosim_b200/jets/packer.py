@@ -16,6 +16,7 @@ host.
 
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 
 import numpy as np
@@ -77,6 +78,49 @@ def _mojave_flux():
 
 
 def pack_jets(n: int, size: int, num_jet_components=(3, 10), scaling="normalize") -> JetBatch:
+    """Parameters of ``n`` jets from the global legacy ``np.random`` stream.
+
+    The draws are made by the native packer (``rsb_jet_pack``: the stream's state is handed over
+    and written back) unless ``scaling="mojave"`` needs scipy's beta draw, the component range
+    exceeds the native limit, or ``RSB_PY_PACKER=1`` asks for :func:`pack_jets_py`.
+    """
+    lo, hi = int(num_jet_components[0]), int(num_jet_components[1])
+    if scaling != "mojave" and 2 <= lo <= hi <= 32 and os.environ.get("RSB_PY_PACKER") != "1":
+        return _pack_jets_native(n, size, lo, hi)
+    return pack_jets_py(n, size, num_jet_components, scaling)
+
+
+def _pack_jets_native(n: int, size: int, lo: int, hi: int) -> JetBatch:
+    import ctypes as C
+
+    from .. import _lib as L
+
+    slots = 2 * hi - 1
+    params = np.empty((n, slots, 6))
+    extra = np.empty((n, slots, 2))
+    zoom_pad = np.empty(n, dtype=np.int32)
+    zoom_out = np.empty(n)
+    name, key, pos, has_gauss, cached = np.random.get_state()
+    assert name == "MT19937"
+    key = np.ascontiguousarray(key, dtype=np.uint32).copy()
+    c_pos, c_has, c_cached = C.c_int32(int(pos)), C.c_int32(int(has_gauss)), C.c_double(float(cached))
+    counts = np.zeros(3, dtype=np.int64)
+    L.check(
+        L.lib().rsb_jet_pack(
+            key.ctypes.data, C.byref(c_pos), C.byref(c_has), C.byref(c_cached), n, size, lo, hi,
+            params.ctypes.data, extra.ctypes.data, zoom_pad.ctypes.data, zoom_out.ctypes.data,
+            counts.ctypes.data,
+        ),
+        "rsb_jet_pack",
+    )
+    np.random.set_state((name, key, c_pos.value, c_has.value, c_cached.value))
+    batch = JetBatch(size, slots, params, extra, zoom_pad, zoom_out)
+    batch.border_counts = counts
+    return batch
+
+
+def pack_jets_py(n: int, size: int, num_jet_components=(3, 10), scaling="normalize") -> JetBatch:
+    """Pure-numpy restatement of the same draws (the native packer's check, and the mojave path)."""
     lo, hi = int(num_jet_components[0]), int(num_jet_components[1])
     slots = 2 * hi - 1
     params = np.zeros((n, slots, 6))

@@ -4,20 +4,25 @@ import numpy as np
 import pytest
 
 from oracle import jet as ojet
-from radiosim_b200.jets.packer import pack_jets, source_lists
+from radiosim_b200.jets.packer import pack_jets, pack_jets_py, source_lists
 
 
+@pytest.mark.parametrize("impl", ["native", "python"])
 @pytest.mark.parametrize("size,scaling,seed", [(128, "normalize", 1337), (64, "normalize", 3),
                                                (200, "mojave", 5), (256, "normalize", 11)])
-def test_packer_matches_oracle_stream(size, scaling, seed):
+def test_packer_matches_oracle_stream(size, scaling, seed, impl):
+    """pack_jets (native rsb_jet_pack; numpy restatement for "mojave") and pack_jets_py against the
+    oracle: same draws in the same order, same zoom decisions; list targets bit-identical for the
+    numpy restatement and within 2 ulp for the native packer (libm vs numpy's SIMD exp/sin/cos)."""
     n = 24
+    packer = pack_jets if impl == "native" else pack_jets_py
     np.random.seed(seed)
     trace = []
     _, y = ojet.create_jet((n, 3, size, size), (3, 10), scaling, "list", trace=trace)
     end_oracle = np.random.rand()
 
     np.random.seed(seed)
-    b = pack_jets(n, size, (3, 10), scaling)
+    b = packer(n, size, (3, 10), scaling)
     end_packer = np.random.rand()
     assert end_packer == end_oracle  # same number of draws, same order
 
@@ -31,7 +36,43 @@ def test_packer_matches_oracle_stream(size, scaling, seed):
     margin = np.array([t["margin"] for t in trace])
     peak = np.array([t["jet_max"] for t in trace])
     out = source_lists(b, margin, peak, scaling == "normalize")
-    assert np.array_equal(out, y)
+    if impl == "python" or scaling == "mojave":
+        assert np.array_equal(out, y)
+    else:
+        assert hasattr(b, "border_counts")  # the native path really ran
+        assert np.allclose(out, y, rtol=1e-15, atol=0) and np.array_equal(out == 0, y == 0)
+
+
+@pytest.mark.parametrize("size,n,seed,comps", [(256, 300, 1, (3, 10)), (128, 300, 7, (3, 10)), (64, 200, 3, (2, 6)),
+                                               (101, 100, 11, (3, 10)), (32, 100, 4, (4, 4))])
+def test_native_packer_continues_the_numpy_stream(size, n, seed, comps):
+    """rsb_jet_pack against the numpy restatement: generator state (key, position, cached gaussian)
+    identical afterwards, every branch identical, floats within 2 ulp."""
+    np.random.seed(seed)
+    np.random.normal()  # leave a cached second gaussian in the state that is handed over
+    a = pack_jets(n, size, comps)
+    sa = np.random.get_state()
+    np.random.seed(seed)
+    np.random.normal()
+    b = pack_jets_py(n, size, comps)
+    sb = np.random.get_state()
+    assert sa[0] == sb[0] and np.array_equal(sa[1], sb[1]) and sa[2:] == sb[2:]
+    assert np.array_equal(a.zoom_pad, b.zoom_pad) and np.array_equal(a.zoom_out, b.zoom_out)
+    for u, v in ((a.params, b.params), (a.extra, b.extra)):
+        assert np.array_equal(u == 0, v == 0)
+        assert np.allclose(u, v, rtol=1e-15, atol=0)
+    assert a.border_counts.sum() == n
+
+
+def test_native_packer_rejects_bad_arguments():
+    from radiosim_b200 import _lib as L
+    import ctypes as C
+    key = np.zeros(624, dtype=np.uint32)
+    pos, has, cached = C.c_int32(700), C.c_int32(0), C.c_double(0.0)
+    out = np.zeros(64)
+    rc = L.lib().rsb_jet_pack(key.ctypes.data, C.byref(pos), C.byref(has), C.byref(cached), 1, 64, 3, 10,
+                              out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data, None)
+    assert rc > 0 and b"position" in L.lib().rsb_last_error()
 
 
 def test_packer_slot_layout():
