@@ -158,17 +158,47 @@ class DeviceBuffer:
         return out
 
 
+# Page-locked blocks are expensive to create (the driver pins every page: ~0.3 s per GB) and the
+# drop-in functions return arrays backed by them, so released blocks are kept for the next call
+# instead of being handed back to the driver -- up to RSB_PINNED_POOL_MB (default 4096) in total.
+_POOL: list = []          # [(nbytes, ptr)]
+_POOL_CAP = int(os.environ.get("RSB_PINNED_POOL_MB", "4096")) << 20
+
+
+def _pool_take(nbytes: int):
+    best = None
+    for i, (sz, _) in enumerate(_POOL):
+        if nbytes <= sz <= max(2 * nbytes, nbytes + (1 << 20)) and (best is None or sz < _POOL[best][0]):
+            best = i
+    return _POOL.pop(best) if best is not None else None
+
+
+def pinned_pool_clear() -> None:
+    """Return every cached page-locked block to the driver."""
+    while _POOL:
+        _, ptr = _POOL.pop()
+        _lib.rsb_free_host(ptr)
+
+
 class _PinnedOwner:
     def __init__(self, nbytes):
+        nbytes = max(int(nbytes), 1)
+        got = _pool_take(nbytes)
+        if got is not None:
+            self.nbytes, self.ptr = got
+            return
         p = _vp()
-        check(_lib.rsb_malloc_host(C.byref(p), int(nbytes)), "rsb_malloc_host")
+        check(_lib.rsb_malloc_host(C.byref(p), nbytes), "rsb_malloc_host")
         self.ptr = p.value
-        self.nbytes = int(nbytes)
+        self.nbytes = nbytes
 
     def __del__(self):
         try:
             if self.ptr:
-                _lib.rsb_free_host(self.ptr)
+                if sum(sz for sz, _ in _POOL) + self.nbytes <= _POOL_CAP:
+                    _POOL.append((self.nbytes, self.ptr))
+                else:
+                    _lib.rsb_free_host(self.ptr)
                 self.ptr = None
         except Exception:
             pass

@@ -89,11 +89,12 @@ def create_jet(grid, conf):
     normalize = scaling == "normalize"
     img, margin, peak, planes = render_batch(batch, normalize, planes=(ttype == "gauss"))
     slist = source_lists(batch, margin, peak, normalize)
-    jets = np.array(img)[:, None, :, :]
+    jets = img[:, None, :, :]  # (page-locked block owned by the array; recycled when it is released)
     if ttype == "list":
         targets = slist
     elif ttype == "clean":
-        targets = jets.copy()
+        targets = L.pinned_empty(jets.shape, jets.dtype)
+        np.copyto(targets, jets)
     elif ttype == "gauss":
         targets = np.empty((n, batch.slots + 2, size, size))
         targets[:, : batch.slots] = planes
