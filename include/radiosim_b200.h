@@ -245,6 +245,19 @@ int rsb_jet_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* 
                  int n, int size, int comp_lo, int comp_hi, double* params, double* extra,
                  int32_t* zoom_pad, double* zoom_out, long long* border_counts);
 
+/* The source loop of create_survey, reference src/radiosim/survey/survey.py:49-107 (class draw,
+ * sub-jet size / position and its nested create_jet chain, wide and narrow Gaussians), on the same
+ * legacy stream and with the same state hand-over as rsb_jet_pack.  class_dist [3] f64.  Buffers
+ * sized for n*num_sources entries: src [.., 6] f64 (per image: wide rows, then narrow rows),
+ * src_offs [n, 3] i32 (first wide, first narrow, end), and per sub-jet in draw order jet_params
+ * [.., 2*comp_hi-1, 6] f64, jet_zoom_pad, jet_size, jet_image, jet_row0, jet_col0 (i32; corner of
+ * the paste, survey.py:61-76); *njets_out = sub-jets drawn.  2 <= comp_lo <= comp_hi <= 32. */
+int rsb_survey_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
+                    int n, int size, int num_sources, const double* class_dist, int scale_sources,
+                    int comp_lo, int comp_hi, double* src, int32_t* src_offs, double* jet_params,
+                    int32_t* jet_zoom_pad, int32_t* jet_size, int32_t* jet_image, int32_t* jet_row0,
+                    int32_t* jet_col0, int32_t* njets_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,6 +19,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <new>
 
 #include "common.cuh"
 
@@ -181,6 +182,89 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
   return !nan && m < thr;
 }
 
+// One image of create_jet's chain (jet.py:54-125 and the draw at :168) on generator g.
+// p [2*hi-1, 6], ex [2*hi-1, 2].
+inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, double* ex, int32_t* zoom_pad,
+                         double* zoom_out, long long* counts) {
+  const int slots = 2 * hi - 1;
+  const double pi = 3.141592653589793, N = (double)size;
+  const int mid = size / 2;
+  double amp[kMaxHi] = {0}, x[kMaxHi] = {0}, y[kMaxHi] = {0}, sx[kMaxHi] = {0}, sy[kMaxHi] = {0},
+         rot[kMaxHi] = {0}, beta[kMaxHi] = {0};
+  const int k = (int)g.randint(comp_lo, (int64_t)hi + 1);
+  rot[0] = g.uniform(0.0, pi);
+  const double beta1 = g.uniform(0.0, 1.0);
+  if (hi > 1) beta[1] = beta1;
+  double bend = g.uniform(0.0, pi);
+  const double tilt = g.uniform(0.0, pi / 2);
+  const double sin_tilt = std::sin(tilt);
+  for (int i = 0; i < k; ++i) {
+    amp[i] = std::exp(-std::sqrt((double)i) * g.normal(1.3, 0.2));
+    if (i >= 1 && g.sample() < 0.1) amp[i] = 0.0;
+    if (i >= 2) beta[i] = beta[1] * std::exp(-std::sqrt((double)(i - 1)) * g.normal(0.5, 0.1));
+    bend += g.normal(0.0, pi / 24);
+    const double cb = std::cos(bend), sb = std::sin(bend);
+    const double acb = std::fabs(cb), asb = std::fabs(sb);
+    const double fill = acb < asb ? 1.0 / asb : (acb > asb ? 1.0 / acb : std::sqrt(2.0));
+    const double dist = (double)i / (double)(k - 1) * N / 2 * fill * sin_tilt * 0.7;
+    x[i] = dist * cb + mid;
+    y[i] = dist * sb + mid;
+    const double num = N / (double)k * fill * std::sqrt((double)(i + 1));
+    const double p0 = num / g.uniform(3.0, 8.0), p1 = num / g.uniform(3.0, 8.0);
+    if (p0 >= p1) { sx[i] = p0; sy[i] = p1; } else { sx[i] = p1; sy[i] = p0; }
+    if (i >= 1) rot[i] = rot[i - 1] + g.normal(0.0, pi / 18);
+  }
+  const double mu = std::cos(tilt);
+  const double off_x = g.uniform(-N / 20, N / 20), off_y = g.uniform(-N / 20, N / 20);
+  std::memset(p, 0, sizeof(double) * slots * 6);
+  std::memset(ex, 0, sizeof(double) * slots * 2);
+  double away[kMaxHi];
+  for (int i = 0; i < hi; ++i) {
+    const double lorentz = 1.0 / std::sqrt(1.0 - beta[i] * beta[i]);
+    const double toward = 1.0 / (lorentz * (1.0 - beta[i] * mu));
+    away[i] = 1.0 / (lorentz * (1.0 + beta[i] * mu));
+    p[i * 6 + 0] = amp[i] * toward;
+    p[i * 6 + 1] = x[i] + off_x;
+    p[i * 6 + 2] = y[i] + off_y;
+    p[i * 6 + 3] = sx[i];
+    p[i * 6 + 4] = sy[i];
+    p[i * 6 + 5] = rot[i];
+    ex[i * 2 + 1] = beta[i];
+  }
+  for (int s = 0; s < slots; ++s) ex[s * 2] = tilt;
+  if (g.sample() < 0.3) {  // counter jet: mirror slots 1.. through the image centre
+    for (int i = 1; i < hi; ++i) {
+      double* q = p + (size_t)(hi + i - 1) * 6;
+      q[0] = amp[i] * away[i];
+      q[1] = N - x[i] + off_x;
+      q[2] = N - y[i] + off_y;
+      q[3] = sx[i];
+      q[4] = sy[i];
+      q[5] = rot[i];
+      ex[(hi + i - 1) * 2 + 1] = beta[i];
+    }
+  }
+  SlotRot sr[2 * kMaxHi];
+  for (int s = 0; s < slots; ++s) {
+    const double* q = p + (size_t)s * 6;
+    sr[s].amp = q[0];
+    if (q[0] == 0.0) continue;
+    sr[s].cs = std::cos(q[5]);
+    sr[s].sn = std::sin(q[5]);
+    sr[s].ra = q[2] * sr[s].cs - q[1] * sr[s].sn;
+    sr[s].rb = q[2] * sr[s].sn + q[1] * sr[s].cs;
+    sr[s].wx = q[3];
+    sr[s].wy = q[4];
+  }
+  *zoom_pad = -1;
+  *zoom_out = 1.0;
+  if (border_below(sr, slots, size, counts)) {
+    const double zo = g.uniform(0.5, 1.0);
+    *zoom_out = zo;
+    *zoom_pad = (int32_t)(int64_t)((1.0 / zo - 1.0) * N / 2);
+  }
+}
+
 }  // namespace pack
 }  // namespace rsb
 
@@ -197,87 +281,106 @@ extern "C" int rsb_jet_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gaus
   Legacy g{mt_key, *mt_pos, *has_gauss, *cached_gauss};
   long long counts_local[3] = {0, 0, 0};
   long long* counts = border_counts ? border_counts : counts_local;
-  const int hi = comp_hi, slots = 2 * hi - 1;
+  const int slots = 2 * comp_hi - 1;
+  for (int b = 0; b < n; ++b)
+    pack_one_jet(g, size, comp_lo, comp_hi, params + (size_t)b * slots * 6, extra + (size_t)b * slots * 2,
+                 zoom_pad + b, zoom_out + b, counts);
+  *mt_pos = g.pos;
+  *has_gauss = g.has_gauss;
+  *cached_gauss = g.gauss;
+  return 0;
+}
+
+// The source loop of create_survey (reference src/radiosim/survey/survey.py:49-107) on the same
+// legacy stream: class by uniform(0, sum dist); class 0 draws a sub-jet (size, position, then the
+// whole create_jet chain on size x size, border test included); classes 1 and 2 draw a wide or
+// a narrow Gaussian.  Outputs are sized for the worst case (every source of one class):
+//   src [n*num_sources, 6] (amp, x, y, sx, sy, rot): per image the wide rows, then the narrow
+//   ones; src_offs [n, 3] = first wide row, first narrow row, end;
+//   jet_* [n*num_sources]: sub-jets in draw order (parameters [.., 2*comp_hi-1, 6], zoom pad,
+//   size, image index, row and column of the paste's corner: floor(pos - size/2)).
+extern "C" int rsb_survey_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
+                               int n, int size, int num_sources, const double* class_dist, int scale_sources,
+                               int comp_lo, int comp_hi, double* src, int32_t* src_offs, double* jet_params,
+                               int32_t* jet_zoom_pad, int32_t* jet_size, int32_t* jet_image,
+                               int32_t* jet_row0, int32_t* jet_col0, int32_t* njets_out) {
+  using namespace rsb::pack;
+  RSB_ARG(mt_key && mt_pos && has_gauss && cached_gauss, "rsb_survey_pack: NULL generator state");
+  RSB_ARG(class_dist && src && src_offs && jet_params && jet_zoom_pad && jet_size && jet_image && jet_row0 &&
+              jet_col0 && njets_out, "rsb_survey_pack: NULL buffer");
+  RSB_ARG(n >= 0 && size >= 2 && num_sources >= 0, "rsb_survey_pack: bad n / size / num_sources (%d, %d, %d)",
+          n, size, num_sources);
+  RSB_ARG(comp_lo >= 2 && comp_lo <= comp_hi && comp_hi <= kMaxHi,
+          "rsb_survey_pack: components must satisfy 2 <= lo <= hi <= %d (got %d, %d)", kMaxHi, comp_lo, comp_hi);
+  RSB_ARG(*mt_pos >= 0 && *mt_pos <= 624, "rsb_survey_pack: generator position %d out of range", *mt_pos);
+  Legacy g{mt_key, *mt_pos, *has_gauss, *cached_gauss};
+  long long counts[3] = {0, 0, 0};
+  const int slots = 2 * comp_hi - 1;
   const double pi = 3.141592653589793, N = (double)size;
-  const int mid = size / 2;
+  const double total = class_dist[0] + class_dist[1] + class_dist[2];
+  const double c01 = class_dist[0] + class_dist[1];
+  double* narrow = new (std::nothrow) double[(size_t)(num_sources > 0 ? num_sources : 1) * 6];
+  RSB_ARG(narrow != nullptr, "rsb_survey_pack: out of host memory");
+  double extra_unused[2 * (2 * kMaxHi)];
+  double zoom_out_unused;
+  int nj = 0;
+  int64_t row = 0;
   for (int b = 0; b < n; ++b) {
-    double amp[kMaxHi] = {0}, x[kMaxHi] = {0}, y[kMaxHi] = {0}, sx[kMaxHi] = {0}, sy[kMaxHi] = {0},
-           rot[kMaxHi] = {0}, beta[kMaxHi] = {0};
-    const int k = (int)g.randint(comp_lo, (int64_t)hi + 1);
-    rot[0] = g.uniform(0.0, pi);
-    const double beta1 = g.uniform(0.0, 1.0);
-    if (hi > 1) beta[1] = beta1;
-    double bend = g.uniform(0.0, pi);
-    const double tilt = g.uniform(0.0, pi / 2);
-    const double sin_tilt = std::sin(tilt);
-    for (int i = 0; i < k; ++i) {
-      amp[i] = std::exp(-std::sqrt((double)i) * g.normal(1.3, 0.2));
-      if (i >= 1 && g.sample() < 0.1) amp[i] = 0.0;
-      if (i >= 2) beta[i] = beta[1] * std::exp(-std::sqrt((double)(i - 1)) * g.normal(0.5, 0.1));
-      bend += g.normal(0.0, pi / 24);
-      const double cb = std::cos(bend), sb = std::sin(bend);
-      const double acb = std::fabs(cb), asb = std::fabs(sb);
-      const double fill = acb < asb ? 1.0 / asb : (acb > asb ? 1.0 / acb : std::sqrt(2.0));
-      const double dist = (double)i / (double)(k - 1) * N / 2 * fill * sin_tilt * 0.7;
-      x[i] = dist * cb + mid;
-      y[i] = dist * sb + mid;
-      const double num = N / (double)k * fill * std::sqrt((double)(i + 1));
-      const double p0 = num / g.uniform(3.0, 8.0), p1 = num / g.uniform(3.0, 8.0);
-      if (p0 >= p1) { sx[i] = p0; sy[i] = p1; } else { sx[i] = p1; sy[i] = p0; }
-      if (i >= 1) rot[i] = rot[i - 1] + g.normal(0.0, pi / 18);
-    }
-    const double mu = std::cos(tilt);
-    const double off_x = g.uniform(-N / 20, N / 20), off_y = g.uniform(-N / 20, N / 20);
-    double* p = params + (size_t)b * slots * 6;
-    double* ex = extra + (size_t)b * slots * 2;
-    std::memset(p, 0, sizeof(double) * slots * 6);
-    std::memset(ex, 0, sizeof(double) * slots * 2);
-    double away[kMaxHi];
-    for (int i = 0; i < hi; ++i) {
-      const double lorentz = 1.0 / std::sqrt(1.0 - beta[i] * beta[i]);
-      const double toward = 1.0 / (lorentz * (1.0 - beta[i] * mu));
-      away[i] = 1.0 / (lorentz * (1.0 + beta[i] * mu));
-      p[i * 6 + 0] = amp[i] * toward;
-      p[i * 6 + 1] = x[i] + off_x;
-      p[i * 6 + 2] = y[i] + off_y;
-      p[i * 6 + 3] = sx[i];
-      p[i * 6 + 4] = sy[i];
-      p[i * 6 + 5] = rot[i];
-      ex[i * 2 + 1] = beta[i];
-    }
-    for (int s = 0; s < slots; ++s) ex[s * 2] = tilt;
-    if (g.sample() < 0.3) {  // counter jet: mirror slots 1.. through the image centre
-      for (int i = 1; i < hi; ++i) {
-        double* q = p + (size_t)(hi + i - 1) * 6;
-        q[0] = amp[i] * away[i];
-        q[1] = N - x[i] + off_x;
-        q[2] = N - y[i] + off_y;
-        q[3] = sx[i];
-        q[4] = sy[i];
-        q[5] = rot[i];
-        ex[(hi + i - 1) * 2 + 1] = beta[i];
+    const int64_t first = row;
+    int nnarrow = 0;
+    for (int q = 0; q < num_sources; ++q) {
+      const double u = g.uniform(0.0, total);
+      if (u < class_dist[0]) {
+        const int64_t lo = scale_sources ? (int64_t)(N / 10.24) : 100, hi = scale_sources ? (int64_t)(N / 5.12) : 200;
+        const int js = (int)g.randint(lo, hi);
+        const double pa = g.sample() * N, pb = g.sample() * N;
+        if (js < 2) {
+          delete[] narrow;
+          RSB_ARG(false, "rsb_survey_pack: sub-jet size %d too small (image size %d)", js, size);
+        }
+        pack_one_jet(g, js, comp_lo, comp_hi, jet_params + (size_t)nj * slots * 6, extra_unused,
+                     jet_zoom_pad + nj, &zoom_out_unused, counts);
+        jet_size[nj] = js;
+        jet_image[nj] = b;
+        jet_row0[nj] = (int32_t)std::floor(pa - (double)js / 2);
+        jet_col0[nj] = (int32_t)std::floor(pb - (double)js / 2);
+        ++nj;
+      } else {
+        const bool wide = u < c01;
+        double sx, sy;
+        if (wide) {
+          if (scale_sources) {
+            sx = N * g.uniform(1 / 40.96, 1 / 20.48);
+            sy = sx + g.normal(0.0, N / 204.8);
+          } else {
+            sx = g.uniform(25.0, 50.0);
+            sy = sx + g.normal(0.0, 5.0);
+          }
+        } else {
+          if (scale_sources) {
+            sx = N * g.uniform(1 / 204.8, 1 / 102.4);
+            sy = sx + g.normal(0.0, N / 1024);
+          } else {
+            sx = g.uniform(5.0, 10.0);
+            sy = sx + g.normal(0.0, 1.0);
+          }
+        }
+        const double px = g.sample() * N, py = g.sample() * N;
+        const double amp = g.sample();
+        const double rot = g.uniform(0.0, pi);
+        double* d = wide ? src + (size_t)(row++) * 6 : narrow + (size_t)(nnarrow++) * 6;
+        d[0] = amp; d[1] = px; d[2] = py; d[3] = sx; d[4] = sy; d[5] = rot;
       }
     }
-    SlotRot sr[2 * kMaxHi];
-    for (int s = 0; s < slots; ++s) {
-      const double* q = p + (size_t)s * 6;
-      sr[s].amp = q[0];
-      if (q[0] == 0.0) continue;
-      sr[s].cs = std::cos(q[5]);
-      sr[s].sn = std::sin(q[5]);
-      sr[s].ra = q[2] * sr[s].cs - q[1] * sr[s].sn;
-      sr[s].rb = q[2] * sr[s].sn + q[1] * sr[s].cs;
-      sr[s].wx = q[3];
-      sr[s].wy = q[4];
-    }
-    zoom_pad[b] = -1;
-    zoom_out[b] = 1.0;
-    if (border_below(sr, slots, size, counts)) {
-      const double zo = g.uniform(0.5, 1.0);
-      zoom_out[b] = zo;
-      zoom_pad[b] = (int32_t)(int64_t)((1.0 / zo - 1.0) * N / 2);
-    }
+    const int64_t mid = row;
+    std::memcpy(src + (size_t)row * 6, narrow, sizeof(double) * 6 * (size_t)nnarrow);
+    row += nnarrow;
+    src_offs[b * 3] = (int32_t)first;
+    src_offs[b * 3 + 1] = (int32_t)mid;
+    src_offs[b * 3 + 2] = (int32_t)row;
   }
+  delete[] narrow;
+  *njets_out = nj;
   *mt_pos = g.pos;
   *has_gauss = g.has_gauss;
   *cached_gauss = g.gauss;

@@ -8,12 +8,13 @@ nested ``create_jet`` chain of class-0 sources.  Device: sub-jets through ``rsb_
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
 
 from .. import _lib as L
-from ..jets.packer import JetBatch, pack_jets
+from ..jets.packer import JetBatch, pack_jets, pack_jets_py
 
 __all__ = ["create_survey", "pack_survey", "render_survey"]
 
@@ -26,15 +27,71 @@ class SurveyBatch:
     n: int
     src_params: np.ndarray          # [total, 6] float64, per image: class 1 rows then class 2 rows
     src_offs: np.ndarray            # [n, 3] int32
-    jets: list = field(default_factory=list)        # JetBatch (one jet each), in draw order
+    jets: list = field(default_factory=list)        # JetBatch (one jet each), in draw order (numpy packer)
     jet_image: np.ndarray = None    # [njets] image index
     jet_row0: np.ndarray = None
     jet_col0: np.ndarray = None
+    # the same sub-jets as flat arrays (native packer fills these directly)
+    jet_params: np.ndarray = None   # [njets, slots, 6] float64
+    jet_zoom_pad: np.ndarray = None  # [njets] int32
+    jet_sizes: np.ndarray = None    # [njets] int64
+
+    @property
+    def njets(self) -> int:
+        return len(self.jet_image)
+
+    def flat_jets(self):
+        if self.jet_params is None:
+            slots = self.jets[0].slots if self.jets else 1
+            self.jet_params = (np.concatenate([j.params for j in self.jets]) if self.jets
+                               else np.zeros((0, slots, 6)))
+            self.jet_zoom_pad = (np.concatenate([j.zoom_pad for j in self.jets]) if self.jets
+                                 else np.zeros(0, np.int32))
+            self.jet_sizes = np.array([j.size for j in self.jets], dtype=np.int64)
+        return self.jet_params, self.jet_zoom_pad, self.jet_sizes
 
 
 def pack_survey(n: int, size: int, num_sources: int, class_distribution, scale_sources: bool,
                 num_jet_components=(3, 10), jet_scaling="normalize") -> SurveyBatch:
-    """Consume the global ``np.random`` stream exactly like ``survey.py:49-107``."""
+    """Consume the global ``np.random`` stream exactly like ``survey.py:49-107``: natively
+    (``rsb_survey_pack``) unless the sub-jets need scipy's draw (``jet_scaling="mojave"``), the
+    component range exceeds the native limit, or ``RSB_PY_PACKER=1`` asks for :func:`pack_survey_py`."""
+    lo, hi = int(num_jet_components[0]), int(num_jet_components[1])
+    if (jet_scaling != "mojave" and 2 <= lo <= hi <= 32 and len(class_distribution) == 3
+            and os.environ.get("RSB_PY_PACKER") != "1"):
+        return _pack_survey_native(n, size, int(num_sources), class_distribution, bool(scale_sources), lo, hi)
+    return pack_survey_py(n, size, num_sources, class_distribution, scale_sources, num_jet_components, jet_scaling)
+
+
+def _pack_survey_native(n, size, num_sources, class_distribution, scale_sources, lo, hi) -> SurveyBatch:
+    slots = 2 * hi - 1
+    cap = max(n * num_sources, 1)
+    src = np.empty((cap, 6))
+    offs = np.zeros((n, 3), dtype=np.int32)
+    jp = np.empty((cap, slots, 6))
+    jz, jsz, jimg, jr0, jc0 = (np.empty(cap, dtype=np.int32) for _ in range(5))
+    nj = C.c_int32(0)
+    dist = np.asarray(class_distribution, dtype=np.float64)
+    name, key, pos, has_gauss, cached = np.random.get_state()
+    key = np.ascontiguousarray(key, dtype=np.uint32).copy()
+    c_pos, c_has, c_cached = C.c_int32(int(pos)), C.c_int32(int(has_gauss)), C.c_double(float(cached))
+    L.check(
+        L.lib().rsb_survey_pack(
+            key.ctypes.data, C.byref(c_pos), C.byref(c_has), C.byref(c_cached), n, size, num_sources,
+            dist.ctypes.data, int(scale_sources), lo, hi, src.ctypes.data, offs.ctypes.data, jp.ctypes.data,
+            jz.ctypes.data, jsz.ctypes.data, jimg.ctypes.data, jr0.ctypes.data, jc0.ctypes.data, C.byref(nj)),
+        "rsb_survey_pack",
+    )
+    np.random.set_state((name, key, c_pos.value, c_has.value, c_cached.value))
+    k = nj.value
+    total = int(offs[-1, 2]) if n else 0
+    return SurveyBatch(size, n, src[:total], offs, [], jimg[:k].astype(np.int64), jr0[:k].astype(np.int64),
+                       jc0[:k].astype(np.int64), jp[:k], jz[:k], jsz[:k].astype(np.int64))
+
+
+def pack_survey_py(n: int, size: int, num_sources: int, class_distribution, scale_sources: bool,
+                   num_jet_components=(3, 10), jet_scaling="normalize") -> SurveyBatch:
+    """Pure-numpy restatement of the same draws (the native packer's check, and the mojave path)."""
     rnd = np.random
     total = sum(class_distribution)
     rows, offs = [], np.zeros((n, 3), dtype=np.int32)
@@ -50,7 +107,7 @@ def pack_survey(n: int, size: int, num_sources: int, class_distribution, scale_s
                 else:
                     js = rnd.randint(100, 200)
                 pa, pb = rnd.rand(2) * size
-                jets.append(pack_jets(1, js, num_jet_components, jet_scaling))
+                jets.append(pack_jets_py(1, js, num_jet_components, jet_scaling))
                 jimg.append(b)
                 jr0.append(int(np.floor(pa - js / 2)))
                 jc0.append(int(np.floor(pb - js / 2)))
@@ -84,41 +141,43 @@ def pack_survey(n: int, size: int, num_sources: int, class_distribution, scale_s
 
 
 def _render_subjets(batch: SurveyBatch, normalize: bool):
-    """All sub-jets, grouped by size, into one packed float32 device buffer."""
+    """All sub-jets, grouped by size, into one packed float32 device buffer.
+
+    One upload of the parameters (sorted by size), one launch per distinct size on slices of it."""
     lib = L.lib()
-    nj = len(batch.jets)
-    sizes = np.array([j.size for j in batch.jets], dtype=np.int64)
+    all_params, all_zpad, sizes = batch.flat_jets()
+    nj = batch.njets
     order = np.argsort(sizes, kind="stable")
     pix_off = np.zeros(nj, dtype=np.int64)
-    total_pix = int((sizes.astype(np.int64) ** 2).sum()) + 4 * (len(np.unique(sizes)) + 1)
+    ssz = sizes[order]
+    starts = np.flatnonzero(np.r_[True, ssz[1:] != ssz[:-1]]) if nj else np.zeros(0, np.int64)
+    ends = np.r_[starts[1:], nj] if nj else np.zeros(0, np.int64)
+    total_pix = int((sizes.astype(np.int64) ** 2).sum()) + 4 * (len(starts) + 1)
     d_pix = L.DeviceBuffer(max(total_pix * 4, 16))
-    cursor = 0
+    if nj == 0:
+        return d_pix, pix_off, sizes
+    slots = all_params.shape[1]
+    d_p = L.dev_from(all_params[order])
+    d_z = L.dev_from(all_zpad[order])
+    d_m, d_k = L.DeviceBuffer(nj * 4), L.DeviceBuffer(nj * 8)
+    need_max = 0
+    need = C.c_size_t(0)
+    for a, b in zip(starts, ends):
+        L.check(lib.rsb_jet_workspace_bytes(int(b - a), slots, int(ssz[a]), C.byref(need)))
+        need_max = max(need_max, need.value)
+    d_w = L.DeviceBuffer(max(need_max, 16))
     flags = L.JET_NORMALIZE if normalize else 0
-    keep = []
-    i = 0
-    while i < nj:
-        js = int(sizes[order[i]])
-        j = i
-        while j < nj and sizes[order[j]] == js:
-            j += 1
-        group = order[i:j]
-        params = np.concatenate([batch.jets[g].params for g in group])
-        zpad = np.concatenate([batch.jets[g].zoom_pad for g in group])
-        cnt = len(group)
-        for q, g in enumerate(group):
-            pix_off[g] = cursor + q * js * js
-        need = C.c_size_t(0)
-        L.check(lib.rsb_jet_workspace_bytes(cnt, params.shape[1], js, C.byref(need)))
-        d_p, d_z = L.dev_from(params), L.dev_from(zpad)
-        d_m, d_k = L.DeviceBuffer(cnt * 4), L.DeviceBuffer(cnt * 8)
-        d_w = L.DeviceBuffer(max(need.value, 16))
-        L.check(lib.rsb_jet_render(d_p.ptr, d_z.ptr, cnt, params.shape[1], js, flags,
-                                   d_pix.ptr + cursor * 4, d_m.ptr, d_k.ptr, d_w.ptr, d_w.nbytes, None),
+    cursor = 0
+    for a, b in zip(starts, ends):
+        a, b = int(a), int(b)
+        js, cnt = int(ssz[a]), b - a
+        pix_off[order[a:b]] = cursor + np.arange(cnt, dtype=np.int64) * (js * js)
+        L.check(lib.rsb_jet_render(d_p.ptr + a * slots * 48, d_z.ptr + a * 4, cnt, slots, js, flags,
+                                   d_pix.ptr + cursor * 4, d_m.ptr + a * 4, d_k.ptr + a * 8, d_w.ptr,
+                                   d_w.nbytes, None),
                 "rsb_jet_render (survey sub-jets)")
-        keep.append((d_p, d_z, d_m, d_k, d_w))
         cursor += cnt * js * js
         cursor = (cursor + 3) & ~3  # keep every group 16-byte aligned (128-bit stores)
-        i = j
     L.device_sync()
     return d_pix, pix_off, sizes
 
@@ -128,7 +187,7 @@ def render_survey(batch: SurveyBatch, jet_normalize: bool = True, f64: bool = Tr
     lib = L.lib()
     n, size = batch.n, batch.size
     d_pix, pix_off, sizes = _render_subjets(batch, jet_normalize)
-    nj = len(batch.jets)
+    nj = batch.njets
     rects = np.zeros(max(nj, 1), dtype=JET_RECT)
     jet_offs = np.zeros(n + 1, dtype=np.int32)
     if nj:
@@ -152,8 +211,8 @@ def render_survey(batch: SurveyBatch, jet_normalize: bool = True, f64: bool = Tr
     L.check(lib.rsb_survey_render(d_src.ptr, d_offs.ptr, total, d_rects.ptr, d_joffs.ptr, d_pix.ptr,
                                   n, size, L.JET_OUT_F64 if f64 else 0, d_x.ptr, d_y.ptr, d_w.ptr,
                                   d_w.nbytes, None), "rsb_survey_render")
-    x = d_x.download((n, 1, size, size), dt)
-    y = d_y.download((n, 4, size, size), dt)
+    x = d_x.download((n, 1, size, size), dt, pinned=True)
+    y = d_y.download((n, 4, size, size), dt, pinned=True)
     return x, y
 
 

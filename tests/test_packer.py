@@ -80,3 +80,31 @@ def test_packer_slot_layout():
     b = pack_jets(5, 128, (3, 6))
     assert b.params.shape == (5, 11, 6) and b.zoom_pad.dtype == np.int32
     assert np.all(b.params[:, 0, 0] == 1.0)  # core: amp 1, beta 0 -> boost 1
+
+
+@pytest.mark.parametrize("n,size,nsrc,dist,scale,seed", [
+    (2, 1024, 300, [2, 1, 2], True, 7), (3, 160, 40, [1, 1, 1], True, 8), (2, 512, 100, [2, 1, 2], False, 9),
+    (2, 128, 25, [0, 1, 1], True, 10), (1, 256, 30, [3, 0, 0], True, 11)])
+def test_native_survey_packer_continues_the_numpy_stream(n, size, nsrc, dist, scale, seed):
+    """rsb_survey_pack (survey.py:49-107 incl. the nested create_jet chain) against the numpy
+    restatement: generator state identical afterwards, same sources and sub-jets in the same
+    order, integers exact, floats within 2 ulp."""
+    from radiosim_b200.survey.survey import pack_survey, pack_survey_py
+
+    np.random.seed(seed)
+    np.random.normal()
+    a = pack_survey(n, size, nsrc, dist, scale)
+    sa = np.random.get_state()
+    np.random.seed(seed)
+    np.random.normal()
+    b = pack_survey_py(n, size, nsrc, dist, scale)
+    sb = np.random.get_state()
+    assert a.jets == [] and a.jet_params is not None  # the native path really ran
+    assert np.array_equal(sa[1], sb[1]) and sa[2:] == sb[2:]
+    assert np.array_equal(a.src_offs, b.src_offs) and a.src_params.shape == b.src_params.shape
+    assert np.allclose(a.src_params, b.src_params, rtol=1e-15, atol=0)
+    bp, bz, bs = b.flat_jets()
+    assert a.njets == b.njets and np.array_equal(a.jet_sizes, bs) and np.array_equal(a.jet_zoom_pad, bz)
+    assert np.allclose(a.jet_params, bp, rtol=1e-15, atol=0)
+    for u, v in ((a.jet_image, b.jet_image), (a.jet_row0, b.jet_row0), (a.jet_col0, b.jet_col0)):
+        assert np.array_equal(u, v)
