@@ -241,43 +241,75 @@ def _recipe_compact(rng, size):
     return s
 
 
-def render_sources(sources, size, f64=True, chunk=2048):
-    """Evaluate recipes on the device -> ``[n, size, size]`` float64 (or float32)."""
+def pack_recipes(part, size, pad=True):
+    """Recipes -> the three arrays ``rsb_mojave_render`` takes (records, blobs, 1-D profiles).
+    ``pad=False`` leaves the blob / profile arrays empty when there is no blob (for merging)."""
+    rec = np.zeros(len(part), dtype=RECIPE)
+    blobs, profs = [], []
+    for k, s in enumerate(part):
+        r = rec[k]
+        for q, g in enumerate(s.gauss):
+            r["g"][q] = tuple(g)
+        for q, j in enumerate(s.jets):
+            r["blob0"][q] = len(blobs)
+            r["nblob"][q] = len(j.blobs)
+            r["strength"][q], r["radius"][q] = j.strength, j.radius
+            for b in j.blobs:
+                blobs.append((np.float32(b.amp), 0, 2 * size * len(profs)))
+                profs.append(np.concatenate((b.normal, b.skew)).astype(np.float32))
+        r["angle"], r["amp"] = s.angle, s.amp
+        r["flip1"], r["compact"] = int(s.flip1), int(s.compact)
+    blob_arr = np.array(blobs, dtype=BLOB) if blobs else np.zeros(1 if pad else 0, dtype=BLOB)
+    prof_arr = np.concatenate(profs) if profs else np.zeros(2 * size if pad else 0, dtype=np.float32)
+    return rec, blob_arr, prof_arr
+
+
+def merge_packed(chunks, size):
+    """Concatenate packed chunks, re-basing blob and profile offsets."""
+    recs, blobs, profs = [], [], []
+    nb = npf = 0
+    for rec, b, p in chunks:
+        rec = rec.copy()
+        rec["blob0"] = np.where(rec["nblob"] > 0, rec["blob0"] + nb, 0)  # (unused entries stay 0)
+        b = b.copy()
+        b["prof"] += npf
+        recs.append(rec); blobs.append(b); profs.append(p)
+        nb += len(b)
+        npf += len(p)
+    rec = np.concatenate(recs) if recs else np.zeros(0, dtype=RECIPE)
+    blob_arr = np.concatenate(blobs) if nb else np.zeros(1, dtype=BLOB)
+    prof_arr = np.concatenate(profs) if npf else np.zeros(2 * size, dtype=np.float32)
+    return rec, blob_arr, prof_arr
+
+
+def render_packed(rec, blob_arr, prof_arr, size, f64=True, chunk=2048):
+    """Render packed recipes: slices of the records against the whole blob / profile arrays."""
     L.require_device()
     lib = L.lib()
-    n = len(sources)
+    n = len(rec)
     dt = np.float64 if f64 else np.float32
-    out = np.empty((n, size, size), dtype=dt)
+    out = L.pinned_empty((n, size, size), dt)
     max_imgs = max(1, min(chunk, (1 << 30) // (size * size * 8)))
+    d_b, d_p = L.dev_from(blob_arr), L.dev_from(prof_arr)
     for i0 in range(0, n, max_imgs):
-        part = sources[i0 : i0 + max_imgs]
-        rec = np.zeros(len(part), dtype=RECIPE)
-        blobs, profs = [], []
-        for k, s in enumerate(part):
-            r = rec[k]
-            for q, g in enumerate(s.gauss):
-                r["g"][q] = tuple(g)
-            for q, j in enumerate(s.jets):
-                r["blob0"][q] = len(blobs)
-                r["nblob"][q] = len(j.blobs)
-                r["strength"][q], r["radius"][q] = j.strength, j.radius
-                for b in j.blobs:
-                    blobs.append((np.float32(b.amp), 0, 2 * size * len(profs)))
-                    profs.append(np.concatenate((b.normal, b.skew)).astype(np.float32))
-            r["angle"], r["amp"] = s.angle, s.amp
-            r["flip1"], r["compact"] = int(s.flip1), int(s.compact)
-        blob_arr = np.array(blobs, dtype=BLOB) if blobs else np.zeros(1, dtype=BLOB)
-        prof_arr = np.concatenate(profs) if profs else np.zeros(2 * size, dtype=np.float32)
+        cnt = min(max_imgs, n - i0)
         need = C.c_size_t(0)
-        L.check(lib.rsb_mojave_workspace_bytes(len(part), size, C.byref(need)))
-        d_r, d_b, d_p = L.dev_from(rec), L.dev_from(blob_arr), L.dev_from(prof_arr)
+        L.check(lib.rsb_mojave_workspace_bytes(cnt, size, C.byref(need)))
+        d_r = L.dev_from(rec[i0 : i0 + cnt])
         d_w = L.DeviceBuffer(need.value)
-        d_o = L.DeviceBuffer(len(part) * size * size * np.dtype(dt).itemsize)
-        L.check(lib.rsb_mojave_render(d_r.ptr, len(part), d_b.ptr, d_p.ptr, size,
+        d_o = L.DeviceBuffer(cnt * size * size * np.dtype(dt).itemsize)
+        L.check(lib.rsb_mojave_render(d_r.ptr, cnt, d_b.ptr, d_p.ptr, size,
                                       L.JET_OUT_F64 if f64 else 0, d_o.ptr, d_w.ptr, d_w.nbytes, None),
                 "rsb_mojave_render")
-        out[i0 : i0 + len(part)] = d_o.download((len(part), size, size), dt)
+        dst = out[i0 : i0 + cnt]
+        L.check(lib.rsb_memcpy_d2h(dst.ctypes.data, d_o.ptr, dst.nbytes, None), "d2h")
+        L.device_sync()
     return out
+
+
+def render_sources(sources, size, f64=True, chunk=2048):
+    """Evaluate recipes on the device -> ``[n, size, size]`` float64 (or float32)."""
+    return render_packed(*pack_recipes(sources, size), size, f64=f64, chunk=chunk)
 
 
 def gen_two_jet(rng, size=1024, printout=False):
@@ -319,11 +351,40 @@ def class_counts(class_ratio, bundle_size):
     return amount
 
 
+def _recipe_chunk(kind, children, size):
+    fn = (_recipe_compact, _recipe_one_jet, _recipe_two_jet)[kind]
+    return [fn(c, size) for c in children]
+
+
+def _packed_chunk(kind, children, size):
+    return pack_recipes(_recipe_chunk(kind, children, size), size, pad=False)
+
+
+def make_recipes(rng, amount, size, threads=1):
+    """The host half of ``create_mojave`` ``:56-64``: one recipe per spawned child generator, class
+    after class, returned packed (:func:`pack_recipes`).  The children are independent streams,
+    so ``threads`` > 1 deals them to that many worker processes (the reference hands them to
+    joblib workers); the result does not depend on it."""
+    kids = [rng.spawn(int(a)) for a in amount]  # same spawn order as the reference
+    threads = int(threads)
+    if threads <= 1 or sum(len(k) for k in kids) < 8 * threads:
+        return merge_packed([_packed_chunk(kind, ch, size) for kind, ch in enumerate(kids)], size)
+    import multiprocessing as mp
+
+    jobs = []
+    for kind, ch in enumerate(kids):
+        step = max(1, -(-len(ch) // (4 * threads)))
+        jobs += [(kind, ch[i : i + step], size) for i in range(0, len(ch), step)]
+    with mp.get_context("fork").Pool(threads) as pool:  # the workers never touch the GPU
+        parts = pool.starmap(_packed_chunk, jobs)
+    return merge_packed(parts, size)
+
+
 def create_mojave(conf, rng, today=None):
     """Drop-in for ``create_mojave`` (``:23-81``): ``(data, data_name)``.
 
-    ``general.threads`` is validated like the reference (``:38-42``) but unused: the child
-    generators are consumed in order on the host and rendered in one device batch.
+    ``general.threads`` is validated like the reference (``:38-42``); the recipes of the child
+    generators are drawn on that many host processes and rendered in one device batch.
     """
     threads = conf.general.threads
     if not threads:
@@ -333,13 +394,12 @@ def create_mojave(conf, rng, today=None):
     size = conf.dataset.img_size
     bundle_size = conf.dataset.bundle_size
     amount = class_counts(conf.mojave.class_ratio, bundle_size)
-    sources = [_recipe_compact(c, size) for c in rng.spawn(amount[0])]
-    sources += [_recipe_one_jet(c, size) for c in rng.spawn(amount[1])]
-    sources += [_recipe_two_jet(c, size) for c in rng.spawn(amount[2])]
-    jets = render_sources(sources, size)
+    rec, blob_arr, prof_arr = make_recipes(rng, amount, size, threads)
     classes = np.repeat(np.arange(3), amount)
     order = np.arange(bundle_size)
     rng.shuffle(order)
+    # rendered in shuffled order, so the images need no host-side permutation afterwards
+    jets_shuffled = render_packed(rec[order], blob_arr, prof_arr, size)
     ra = rng.uniform(0, 360, size=bundle_size)      # utils.py:386-390
     dec = rng.uniform(-30, 87, size=bundle_size)
     start = np.datetime64("1995-01-01")             # utils.py:393-406
@@ -349,5 +409,5 @@ def create_mojave(conf, rng, today=None):
         today = datetime.now().date()
     delta = np.datetime64(today) - start
     dates = start + rng.integers(delta.astype(int), size=bundle_size)
-    data = [jets[order], classes[order], ra[order], dec[order], dates.astype("S10")]
+    data = [jets_shuffled, classes[order], ra[order], dec[order], dates.astype("S10")]
     return data, ["galaxies", "galaxy_classes", "RA", "DEC", "date"]

@@ -123,3 +123,16 @@ def test_two_rank_gloo_shards(tmp_path):
             d = read_h5(os.path.join(tmp_path, f))
             assert d["x"].shape == (2, 1, 64, 64) and d["y"].shape == (2, 19, 8)
             assert np.abs(d["x"] - x).max() <= 1e-12 and np.abs(d["y"] - y).max() <= 1e-12
+
+
+def test_mojave_recipes_do_not_depend_on_worker_count():
+    """create_mojave's host half (mojave.py:56-64): the spawned child generators are independent,
+    so dealing them to worker processes must give the very same packed recipes."""
+    from radiosim_b200.mojave.mojave import class_counts, make_recipes
+
+    amount = class_counts([1, 1, 1], 96)
+    a = make_recipes(np.random.default_rng(5), amount, 128, 1)
+    b = make_recipes(np.random.default_rng(5), amount, 128, 3)
+    assert len(a[0]) == 96
+    for u, v in zip(a, b):
+        assert u.dtype == v.dtype and u.tobytes() == v.tobytes()

@@ -77,3 +77,12 @@ d12 = (t[zoom][:, :, 2] - t[zoom][:, :, 1]).astype(float)
 print("stamp 1->2 with candidates %.0f, without %.0f" % (d12[sel].mean() if sel.any() else 0, d12[~sel].mean()))
 tz3 = t[zoom].astype(float)
 print("table: 2->sync %.0f, sync->loop done %.0f, loop done->3 %.0f" % ((tz3[:,:,30]-tz3[:,:,2]).mean(), (tz3[:,:,31]-tz3[:,:,30]).mean(), (tz3[:,:,3]-tz3[:,:,31]).mean()))
+for rk in (0, 1):
+    fw = 2 if rk == 0 else 1
+    fin_w = w[:, rk, fw:, 0] - s0[:, rk, :]
+    last = fin_w.argmax(axis=1) + fw
+    print(f"rank {rk}: last finisher warp histogram", np.bincount(last, minlength=16).tolist())
+    hits_w = w[:, rk, fw:, 2]; tiles_w = w[:, rk, fw:, 1]
+    idx = np.arange(len(last))
+    print(f"   last finisher: hits {hits_w[idx, last - fw].mean():.1f} tiles {tiles_w[idx, last - fw].mean():.2f}  vs mean hits {hits_w.mean():.1f} tiles {tiles_w.mean():.2f};  finish spread by scheduler (warp%4):",
+          [round(float(fin_w[:, [k for k in range(16 - fw) if (k + fw) % 4 == m]].mean())) for m in range(4)])
