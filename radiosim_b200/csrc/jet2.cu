@@ -638,6 +638,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       sm.lbest = 0ull;
       sm.lmargin = N;
       sm.ncand = 0;
+      sm.next_row = 0;
+      sm.foot_lo = N;
+      sm.foot_hi = -1;
+      sm.scale[0] = (double)(N + 2 * max(zpad_next, 0)) / (double)N;  // (zpad_next: this image's pad)
     }
     __syncwarp();
     {
@@ -1008,16 +1012,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       margin = min(margin, (int)exchange(0, (unsigned long long)(unsigned)margin));
       RSB_STAMP(2);
       if (margin >= N) margin = 0;  // empty mask -> idx 0 (argmax of an all-false array)
-      if (tid == 0) {
-        sm.next_row = 0;
-        sm.foot_lo = N;
-        sm.foot_hi = -1;
-        // the two scale factors of the composite operator, once per image
-        sm.scale[0] = (double)(N + 2 * zpad) / (double)N;
-        sm.scale[1] = (double)(N - 2 * margin) / (double)N;
-      }
-      worker_sync();  // foot_* initialised before the atomics below; scale[] visible
-      const double sP = sm.scale[0], sC = sm.scale[1];
+      // the two scale factors of the composite operator: the pad's was computed by thread 0 at
+      // the start of the image (foot_* were reset there too), the crop's needs the margin
+      const double sP = sm.scale[0], sC = (double)(N - 2 * margin) / (double)N;
       RSB_STAMP(30);
 
       // composite tap table (float64 math, float32 weights) + output footprint
