@@ -94,7 +94,7 @@ def create_jet(grid, conf):
         targets = slist
     elif ttype == "clean":
         targets = L.pinned_empty(jets.shape, jets.dtype)
-        np.copyto(targets, jets)
+        L.parallel_copy(targets, jets)
     elif ttype == "gauss":
         targets = np.empty((n, batch.slots + 2, size, size))
         targets[:, : batch.slots] = planes
