@@ -125,7 +125,7 @@ def write_h5(path, datasets: dict) -> None:
             if a.dtype.byteorder == ">":
                 a = a.astype(a.dtype.newbyteorder("<"))
             headers[n] = ("array", a.shape, a.dtype)
-            raws[n] = a.tobytes()
+            raws[n] = memoryview(a.reshape(-1).view(np.uint8)) if a.size else b""  # no copy: written straight from the array
     hdr_off, data_off, gcol_off = {}, {}, {}
     hdr_len = {}
     for n in names:
@@ -138,6 +138,7 @@ def write_h5(path, datasets: dict) -> None:
         hdr_len[n] = hl
         cursor = _pad8(cursor + hl)
     cursor = (cursor + 0x7FF) & ~0x7FF if cursor <= 0x800 else _pad8(cursor)
+    head_len = cursor  # superblock, group structures and object headers; the data follows
     for n in names:
         if headers[n][0] == "vlen":
             gcol_off[n] = cursor
@@ -148,11 +149,12 @@ def write_h5(path, datasets: dict) -> None:
             data_off[n] = cursor
             cursor += 16
         else:
-            data_off[n] = cursor if raws[n] else _UNDEF
-            cursor = _pad8(cursor + len(raws[n]))
+            data_off[n] = cursor if len(raws[n]) else _UNDEF
+            cursor = _pad8(cursor + (raws[n].nbytes if isinstance(raws[n], memoryview) else len(raws[n])))
     eof = cursor
 
-    out = bytearray(eof)
+    out = bytearray(head_len)
+    tail = []  # (file offset, bytes-like) pieces behind the head, in file order
     # superblock v0
     out[0:8] = _SIG
     struct.pack_into("<BBBBBBBxHHI", out, 8, 0, 0, 0, 0, 0, 8, 8, 4, 16, 0)
@@ -182,7 +184,7 @@ def write_h5(path, datasets: dict) -> None:
             nbytes = 16
         else:
             dt_body = _dtype_message(dt)
-            nbytes = len(raws[n])
+            nbytes = raws[n].nbytes if isinstance(raws[n], memoryview) else len(raws[n])
         msgs = [
             _message(0x01, _dataspace_message(shape)),
             _message(0x03, dt_body, flags=1),
@@ -196,16 +198,24 @@ def write_h5(path, datasets: dict) -> None:
             g = gcol_off[n]
             size = gcols[n]
             raw = raws[n]
-            struct.pack_into("<4sB3xQ", out, g, b"GCOL", 1, size)
-            struct.pack_into("<HH4xQ", out, g + 16, 1, 0, len(raw))
-            out[g + 32 : g + 32 + len(raw)] = raw
-            free = g + 32 + _pad8(len(raw))
-            struct.pack_into("<HH4xQ", out, free, 0, 0, g + size - free)
-            struct.pack_into("<IQI", out, data_off[n], len(raw), g, 1)
-        elif raws[n]:
-            out[data_off[n] : data_off[n] + len(raws[n])] = raws[n]
+            col = bytearray(size + 16)  # the collection, then the 16-byte descriptor that is the dataset's data
+            struct.pack_into("<4sB3xQ", col, 0, b"GCOL", 1, size)
+            struct.pack_into("<HH4xQ", col, 16, 1, 0, len(raw))
+            col[32 : 32 + len(raw)] = raw
+            free = 32 + _pad8(len(raw))
+            struct.pack_into("<HH4xQ", col, free, 0, 0, size - free)
+            struct.pack_into("<IQI", col, size, len(raw), g, 1)
+            assert data_off[n] == g + size
+            tail.append((g, col))
+        elif len(raws[n]):
+            tail.append((data_off[n], raws[n]))
     with open(path, "wb") as f:
         f.write(out)
+        for off, piece in tail:
+            f.seek(off)
+            f.write(piece)
+        if f.tell() < eof:
+            f.truncate(eof)
 
 
 # --------------------------------------------------------------------------- reader
