@@ -30,6 +30,32 @@ _DSHARP_POINTINGS = [
 ]
 
 
+class _ShardWriter:
+    """Writes shards on a few background threads while the next bundle is being generated (the
+    file write releases the GIL).  At most ``depth`` bundles are in flight, so their page-locked
+    blocks return to the pool at the rate they are taken."""
+
+    def __init__(self, workers=3, depth=3):
+        from concurrent.futures import ThreadPoolExecutor
+
+        self.pool = ThreadPoolExecutor(workers)
+        self.depth = depth
+        self.pending = []
+
+    def submit(self, path, datasets):
+        while len(self.pending) >= self.depth:
+            self.pending.pop(0).result()
+        self.pending.append(self.pool.submit(write_h5, path, datasets))
+
+    def close(self):
+        try:
+            for f in self.pending:
+                f.result()  # re-raises a writer's exception
+        finally:
+            self.pending = []
+            self.pool.shutdown()
+
+
 def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1):
     """One split: the bundles in ``bundles`` (an iterable of indices) -> one shard each."""
     from ..utils import create_grid
@@ -37,27 +63,33 @@ def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1)
     out = Path(conf.paths.outpath)
     out.mkdir(parents=True, exist_ok=True)
     written = []
-    for i in bundles:
-        path = out / shard_name(mode, opt, i, rank, world)
-        grid = create_grid(conf.dataset.img_size, conf.dataset.bundle_size)
-        if mode == "jet":
-            from ..jets import create_jet
+    sky = target = data = None
+    writer = _ShardWriter()
+    try:
+        for i in bundles:
+            path = out / shard_name(mode, opt, i, rank, world)
+            grid = create_grid(conf.dataset.img_size, conf.dataset.bundle_size)
+            if mode == "jet":
+                from ..jets import create_jet
 
-            sky, target = create_jet(grid, conf)
-            write_h5(path, {"x": sky, "y": target})
-        elif mode == "survey":
-            from ..survey import create_survey
+                sky, target = create_jet(grid, conf)
+                writer.submit(path, {"x": sky, "y": target})
+            elif mode == "survey":
+                from ..survey import create_survey
 
-            sky, target = create_survey(grid, conf)
-            write_h5(path, {"x": sky, "y": target})
-        elif mode == "mojave":
-            from ..mojave import create_mojave
+                sky, target = create_survey(grid, conf)
+                writer.submit(path, {"x": sky, "y": target})
+            elif mode == "mojave":
+                from ..mojave import create_mojave
 
-            data, names = create_mojave(conf, rng)
-            write_h5(path, dict(zip(names, data)))
-        else:
-            raise ValueError(f"Mode {mode} not found. Choose 'survey', 'jet' or 'mojave' in config file")
-        written.append(path)
+                data, names = create_mojave(conf, rng)
+                writer.submit(path, dict(zip(names, data)))
+            else:
+                raise ValueError(f"Mode {mode} not found. Choose 'survey', 'jet' or 'mojave' in config file")
+            sky = target = data = None  # (the writer holds the only references now)
+            written.append(path)
+    finally:
+        writer.close()
     return written
 
 
