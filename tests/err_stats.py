@@ -1,4 +1,6 @@
-"""Error statistics of the CUDA jets against the float64 oracle (images are normalised: peak = 1)."""
+"""Error statistics of the CUDA jets against the float64 oracle (images are normalised: peak = 1).
+
+A test-side script (it imports oracle/, which only tests may do): python tests/err_stats.py on a GPU box."""
 import sys, numpy as np
 sys.path.insert(0, '.')
 from oracle import jet as ojet
