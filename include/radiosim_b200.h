@@ -42,6 +42,10 @@ int rsb_free_host(void* host_ptr);
 int rsb_memset(void* dev_ptr, int value, size_t bytes, void* stream);
 int rsb_memcpy_h2d(void* dev_dst, const void* host_src, size_t bytes, void* stream);
 int rsb_memcpy_d2h(void* host_dst, const void* dev_src, size_t bytes, void* stream);
+/* rows x width_bytes with separate pitches (device planes into a host array that interleaves
+ * them with other planes: the "gauss" targets of create_jet, reference jets/jet.py:219-225) */
+int rsb_memcpy2d_d2h(void* host_dst, size_t dst_pitch, const void* dev_src, size_t src_pitch,
+                     size_t width_bytes, size_t rows, void* stream);
 int rsb_stream_create(void** stream);
 int rsb_stream_destroy(void* stream);
 int rsb_stream_sync(void* stream);

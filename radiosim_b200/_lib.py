@@ -47,6 +47,7 @@ _SIGS = {
     "rsb_memset": ([_vp, _i32, _sz, _vp], _i32),
     "rsb_memcpy_h2d": ([_vp, _vp, _sz, _vp], _i32),
     "rsb_memcpy_d2h": ([_vp, _vp, _sz, _vp], _i32),
+    "rsb_memcpy2d_d2h": ([_vp, _sz, _vp, _sz, _sz, _sz, _vp], _i32),
     "rsb_stream_create": ([C.POINTER(_vp)], _i32),
     "rsb_stream_destroy": ([_vp], _i32),
     "rsb_stream_sync": ([_vp], _i32),

@@ -91,6 +91,12 @@ int rsb_memcpy_d2h(void* dst, const void* src, size_t bytes, void* stream) {
   RSB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   return 0;
 }
+int rsb_memcpy2d_d2h(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes,
+                     size_t rows, void* stream) {
+  RSB_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width_bytes, rows, cudaMemcpyDeviceToHost,
+                             (cudaStream_t)stream));
+  return 0;
+}
 int rsb_stream_create(void** stream) {
   RSB_ARG(stream != nullptr, "rsb_stream_create: NULL out pointer");
   cudaStream_t s;

@@ -17,10 +17,12 @@ from .packer import JetBatch, pack_jets, source_lists
 __all__ = ["apply_train_type", "component_from_list", "create_jet", "render_batch"]
 
 
-def render_batch(batch: JetBatch, normalize: bool, planes: bool = False, f64: bool = True):
+def render_batch(batch: JetBatch, normalize: bool, planes: bool = False, f64: bool = True, planes_out=None):
     """Render a packed batch on the current device through the host-buffer C ABI.
 
     Returns ``(images[n, N, N], margin[n] int32, peak[n] float64, planes or None)``.
+    ``planes_out``: a host array ``[n, P >= slots, N, N]`` of the output dtype (best page-locked)
+    whose first ``slots`` planes per image receive the component planes directly.
     """
     L.require_device()
     n, size, slots = batch.n, batch.size, batch.slots
@@ -41,22 +43,27 @@ def render_batch(batch: JetBatch, normalize: bool, planes: bool = False, f64: bo
         )
     pl = None
     if planes:
-        pl = np.empty((n, slots, size, size), dtype=dt)
-        step = max(1, (256 << 20) // (slots * size * size * pl.itemsize))
+        pl = planes_out if planes_out is not None else L.pinned_empty((n, slots, size, size), dt)
+        assert pl.dtype == dt and pl.shape[0] == n and pl.shape[1] >= slots and pl.flags.c_contiguous
+        img_bytes = slots * size * size * pl.itemsize        # one image's planes on the device
+        host_pitch = pl.shape[1] * size * size * pl.itemsize  # ... and where the next image starts on the host
+        step = max(1, (256 << 20) // img_bytes)
         for i0 in range(0, n, step):
             i1 = min(n, i0 + step)
             d_p = L.dev_from(p[i0:i1])
             d_z = L.dev_from(zp[i0:i1])
             d_m = L.dev_from(np.asarray(margin[i0:i1]))
             d_k = L.dev_from(np.asarray(peak[i0:i1]))
-            d_o = L.DeviceBuffer(pl[i0:i1].nbytes)
+            d_o = L.DeviceBuffer((i1 - i0) * img_bytes)
             L.check(
                 L.lib().rsb_jet_planes(
                     d_p.ptr, d_z.ptr, d_m.ptr, d_k.ptr, i1 - i0, slots, size, flags, d_o.ptr, None
                 ),
                 "rsb_jet_planes",
             )
-            pl[i0:i1] = d_o.download(pl[i0:i1].shape, dt)
+            L.check(L.lib().rsb_memcpy2d_d2h(pl[i0:i1].ctypes.data, host_pitch, d_o.ptr, img_bytes, img_bytes,
+                                             i1 - i0, None), "rsb_memcpy2d_d2h")
+            L.device_sync()
     return img, np.asarray(margin), np.asarray(peak), pl
 
 
@@ -87,7 +94,10 @@ def create_jet(grid, conf):
     ttype = conf.jet.training_type
     batch = pack_jets(n, size, conf.jet.num_jet_components, scaling)
     normalize = scaling == "normalize"
-    img, margin, peak, planes = render_batch(batch, normalize, planes=(ttype == "gauss"))
+    gauss_targets = None
+    if ttype == "gauss":  # planes, background and list plane side by side: the planes land there directly
+        gauss_targets = L.pinned_empty((n, batch.slots + 2, size, size), np.float64)
+    img, margin, peak, planes = render_batch(batch, normalize, planes=(ttype == "gauss"), planes_out=gauss_targets)
     slist = source_lists(batch, margin, peak, normalize)
     jets = img[:, None, :, :]  # (page-locked block owned by the array; recycled when it is released)
     if ttype == "list":
@@ -96,9 +106,8 @@ def create_jet(grid, conf):
         targets = L.pinned_empty(jets.shape, jets.dtype)
         L.parallel_copy(targets, jets)
     elif ttype == "gauss":
-        targets = np.empty((n, batch.slots + 2, size, size))
-        targets[:, : batch.slots] = planes
-        targets[:, batch.slots] = 1 - jets[:, 0]
+        targets = gauss_targets
+        np.subtract(1, jets[:, 0], out=targets[:, batch.slots])
         targets[:, batch.slots + 1] = np.nan
         targets[:, batch.slots + 1, : batch.slots, :8] = slist
     else:

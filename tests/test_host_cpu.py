@@ -63,7 +63,7 @@ def test_shard_ranges_partition():
     assert shard_name("jet", "train", 4, 1, 2) == "data_jet_train_r1_4.h5"
 
 
-def _oracle_render(batch, normalize, planes=False, f64=True):
+def _oracle_render(batch, normalize, planes=False, f64=True, planes_out=None):
     """Stand-in for the CUDA renderer in CPU tests: the oracle on the packed parameters."""
     from oracle import jet as ojet
 
