@@ -183,7 +183,11 @@ def run_cuda(args):
     rank, world = env_int("RANK", 0), env_int("WORLD_SIZE", 1)
     local = env_int("LOCAL_RANK", 0)
     dist = None
+    near = []
     if world > 1:
+        from radiosim_b200.sharder import bind_near_gpu
+
+        near = bind_near_gpu(local)  # host buffers on the GPU's own socket (matters for the e2e leg)
         import torch
         import torch.distributed as dist_mod
 
@@ -314,6 +318,7 @@ def run_cuda(args):
                 "workload": WORKLOAD, "batch_per_gpu": batch, "img_size": SIZE,
                 "slots": SLOTS, "mean_live_components": live_all / (world * batch),
                 "zoom_fraction": zoom_frac, "parallelism": f"dp{world} (independent shards, no collective)",
+                "cpu_binding": f"rank 0 bound to {len(near)} CPUs near its GPU" if near else "none",
                 "l2_policy": f"inputs larger than L2: {batch * SIZE * SIZE * 4 / 2**20:.0f} MiB written per step",
                 "seed": "1337+rank", "packer_images_per_s_per_core": pack_rate,
             },

@@ -32,3 +32,29 @@ def shard_name(mode: str, opt: str, index: int, rank: int, world: int) -> str:
     if world > 1:
         return f"data_{mode}_{opt}_r{rank}_{index}.h5"
     return f"data_{mode}_{opt}_{index}.h5"
+
+
+def bind_near_gpu(local_rank: int) -> list:
+    """Pin this process to the CPUs the driver reports as closest to GPU ``local_rank``.
+
+    With one process per GPU on a multi-socket box, page-locked result buffers then come from the
+    memory of the GPU's own socket and device-to-host copies do not cross the socket link.
+    Returns the CPU list (empty when NVML or the affinity call is unavailable; nothing changes
+    then).  ``RSB_NO_BIND=1`` turns it off."""
+    if os.environ.get("RSB_NO_BIND") == "1" or not hasattr(os, "sched_setaffinity"):
+        return []
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(int(local_rank))
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return []

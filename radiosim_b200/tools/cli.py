@@ -17,7 +17,11 @@ def simulate(argv=None) -> int:
     from .. import _lib as L
     from ..sharder import rank_info
 
-    _, _, local = rank_info()
+    _, world, local = rank_info()
+    if world > 1:  # one process per GPU: keep each one's host buffers on its GPU's socket
+        from ..sharder import bind_near_gpu
+
+        bind_near_gpu(local)
     L.require_device()
     L.set_device(local)
     if args.mode == "ppdisk":
