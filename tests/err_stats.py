@@ -7,7 +7,10 @@ from oracle import jet as ojet
 from radiosim_b200.jets.jet import render_batch
 from radiosim_b200.jets.packer import pack_jets
 worst = 0.0
+import os
+SCALE = int(os.environ.get("RSB_ERR_SCALE", "1"))  # more jets per case
 for size, n, seed in [(128, 48, 1), (200, 32, 2), (256, 64, 3), (256, 64, 11), (64, 48, 5)]:
+    n *= SCALE
     np.random.seed(seed); tr = []
     ox, _ = ojet.create_jet((n, 3, size, size), (3, 10), "normalize", "clean", trace=tr)
     np.random.seed(seed); b = pack_jets(n, size, (3, 10), "normalize")
