@@ -91,12 +91,12 @@ def _htab():
     return _HTAB
 
 
-def render_protos(img_size, packed, chunk=8):
+def render_protos(img_size, packed, chunk=32):
     """``packed``: list of ``pack_proto`` results -> float32 ``[n, img_size, img_size]``."""
     L.require_device()
     lib = L.lib()
     n = len(packed)
-    out = np.empty((n, img_size, img_size), dtype=np.float32)
+    out = L.pinned_empty((n, img_size, img_size), np.float32)
     d_h = L.dev_from(_htab())
     for i0 in range(0, n, chunk):
         part = packed[i0 : i0 + chunk]
@@ -116,7 +116,9 @@ def render_protos(img_size, packed, chunk=8):
         d_o = L.DeviceBuffer(len(part) * img_size * img_size * 4)
         L.check(lib.rsb_ppdisk_render(d_c.ptr, ncomp, d_i.ptr, len(part), d_h.ptr, img_size,
                                       d_o.ptr, d_w.ptr, d_w.nbytes, None), "rsb_ppdisk_render")
-        out[i0 : i0 + len(part)] = d_o.download((len(part), img_size, img_size), np.float32)
+        dst = out[i0 : i0 + len(part)]
+        L.check(lib.rsb_memcpy_d2h(dst.ctypes.data, d_o.ptr, dst.nbytes, None), "d2h")
+        L.device_sync()
     return out
 
 
