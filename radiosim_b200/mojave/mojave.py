@@ -34,6 +34,23 @@ def _as_rng(rng):
     return np.random.default_rng(seed=rng) if isinstance(rng, (int, np.integer)) else rng
 
 
+def _expon_rvs(rng, loc, scale):
+    """``scipy.stats.expon.rvs(loc, scale, random_state=rng)`` without its argument checking
+    (same draw, same arithmetic: ``standard_exponential * scale + loc``)."""
+    return rng.standard_exponential(()) * scale + loc
+
+
+def _skewnorm_rvs(rng, a, loc, scale):
+    """``scipy.stats.skewnorm.rvs(a, loc, scale, random_state=rng)``: scipy's two-normal
+    construction (``skewnorm_gen._rvs``), then ``* scale + loc``."""
+    a = np.float64(a)
+    u0 = rng.normal(size=())
+    v = rng.normal(size=())
+    d = a / np.sqrt(1 + a**2)
+    u1 = d * u0 + v * np.sqrt(1 - d**2)
+    return (u1 if u0 >= 0 else -u1) * scale + loc
+
+
 class _Blob:
     """amp * normal[row] * skew[col] (``src/radiosim/utils/gauss.py:131-148``)."""
 
@@ -51,7 +68,7 @@ class _Blob:
 
     def at(self, r, c):
         v = (self.normal[r] * self.skew[c]) * self.amp
-        return 0.0 if np.isclose(v, 0) else v
+        return 0.0 if abs(v) <= 1e-8 else v  # np.isclose(v, 0) with its default atol, rtol * 0 = 0
 
 
 class _Jet:
@@ -128,9 +145,9 @@ class _Source:
 def _recipe_two_jet(rng, size):
     """``gen_two_jet`` ``:264-398``."""
     dev = 1 + rng.normal(loc=0, scale=0.1, size=5)
-    amp = expon.rvs(1.715e-4, 1.985e-2, random_state=rng)
-    r_w = skewnorm.rvs(4.37, 22.71, 16.85, random_state=rng) / 10
-    r_l = skewnorm.rvs(8.62, 69.60, 54.73, random_state=rng) / 4
+    amp = _expon_rvs(rng, 1.715e-4, 1.985e-2)
+    r_w = _skewnorm_rvs(rng, 4.37, 22.71, 16.85) / 10
+    r_l = _skewnorm_rvs(rng, 8.62, 69.60, 54.73) / 4
     r_amp = amp * rng.power(0.7)
     l_w, l_l, l_amp = r_w * dev[2], r_l * dev[1], r_amp * dev[0]
     dims = np.sort([r_w / 2, r_l / 5, l_w / 2, l_l / 5])
@@ -155,9 +172,9 @@ def _recipe_two_jet(rng, size):
 
 def _recipe_one_jet(rng, size):
     """``gen_one_jet`` ``:401-492``."""
-    amp = expon.rvs(1.715e-4, 1.985e-2, random_state=rng)
-    width = skewnorm.rvs(4.37, 22.71, 16.85, random_state=rng) / 12
-    length = skewnorm.rvs(8.62, 69.60, 54.73, random_state=rng) / 6.5
+    amp = _expon_rvs(rng, 1.715e-4, 1.985e-2)
+    width = _skewnorm_rvs(rng, 4.37, 22.71, 16.85) / 12
+    length = _skewnorm_rvs(rng, 8.62, 69.60, 54.73) / 6.5
     jet_amp = amp * rng.power(0.7)
     dims = np.sort([width / 2, length / 5])
     sx, sy, rot = _core_widths(rng, dims)
@@ -189,10 +206,10 @@ def _recipe_compact(rng, size):
     """``gen_compact`` ``:495-662``."""
     ncomps = rng.integers(1, 4)
     outflow = rng.uniform() > 0.5
-    amp = expon.rvs(5.54e-05, 0.02, random_state=rng)
+    amp = _expon_rvs(rng, 5.54e-05, 0.02)
     jet_amp = amp * rng.normal(2 / 3, 0.05)
-    width = skewnorm.rvs(8.41, 3.04, 3.46, random_state=rng) * 0.8
-    length = skewnorm.rvs(6.04, 3.02, 2.59, random_state=rng) * 1
+    width = _skewnorm_rvs(rng, 8.41, 3.04, 3.46) * 0.8
+    length = _skewnorm_rvs(rng, 6.04, 3.02, 2.59) * 1
     s = _Source(size)
     if outflow:
         jet = _base_jet(size, jet_amp, width, length, 4)

@@ -136,3 +136,17 @@ def test_mojave_recipes_do_not_depend_on_worker_count():
     assert len(a[0]) == 96
     for u, v in zip(a, b):
         assert u.dtype == v.dtype and u.tobytes() == v.tobytes()
+
+
+def test_mojave_direct_draws_equal_scipy():
+    """The recipe code draws expon / skewnorm variates without scipy's rvs wrapper (it costs more
+    than the draw); the values and the stream position must be those of scipy's."""
+    from scipy.stats import expon, skewnorm
+    from radiosim_b200.mojave.mojave import _expon_rvs, _skewnorm_rvs
+
+    r1, r2 = np.random.default_rng(7), np.random.default_rng(7)
+    for _ in range(300):
+        for a, loc, scale in ((4.37, 22.71, 16.85), (8.62, 69.60, 54.73), (8.41, 3.04, 3.46), (6.04, 3.02, 2.59)):
+            assert skewnorm.rvs(a, loc, scale, random_state=r1) == _skewnorm_rvs(r2, a, loc, scale)
+        assert expon.rvs(1.715e-4, 1.985e-2, random_state=r1) == _expon_rvs(r2, 1.715e-4, 1.985e-2)
+    assert r1.random() == r2.random()
