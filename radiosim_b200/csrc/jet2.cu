@@ -1,25 +1,26 @@
 // On-chip jet renderer: the raw image never leaves shared memory.
+// (reference: src/radiosim/jets/jet.py:144-192, utils/gauss.py:50-97, utils/utils.py:90-177)
 //
 // One image per thread-block CLUSTER.  kCluster == 1: the whole raw image sits in one
 // CTA's shared memory (size <= 128).  kCluster == 2: the image is split into two row
 // bands, one per CTA of a 2-CTA cluster (size 256: 129 x 256 floats = 132 KB each);
 // the composite zoom operator is centre preserving, so each CTA resamples its own band
 // and the only data that crosses CTAs is ONE halo row, the margin and the arg-max,
-// written straight into the peer's shared memory (DSMEM) before a cluster barrier.
+// written into the peer's shared memory with st.async (completion on the peer's mbarrier).
 //
-// Per image (see jet.cu for the algorithm and the reference citations):
-//   setup   : 1-D bulk async copy of the parameter block (double buffered).  Warp 0
-//             builds, one image AHEAD and off the critical path, the float32 conic
-//             coefficients and, per component and 8-row group, the exact column
-//             interval of its > tau footprint (the culling table).
-//   phase 1 : warps pull 8-row x 64-column tiles from a shared counter; 16 pixels per
-//             lane, ~6.4 issue slots per MUFU.EX2; a component is skipped when its
-//             column interval for the tile's row group misses the tile.
-//   zoom    : margin (DSMEM atomicMin) -> tap table -> H pass in place, rows pulled
-//             dynamically, column taps in registers -> halo row exchange -> ONE V pass
-//             whose results stay in registers -> arg-max (DSMEM atomicMax) -> scaled
-//             128-bit stores.  The float64 peak for the labels is evaluated by one
-//             warp while the others already render the next image.
+// Per image (DESIGN.md 4.1 has the long version):
+//   ahead   : 1-D bulk async copy of the parameter block (triple buffered).  Warp 0 builds,
+//             one image AHEAD and off the critical path, the float32 conic coefficients,
+//             which slots touch which 8 x 64 tile (box-vs-ellipse test), the frame bound
+//             dlo, and the per-warp work lists (tiles sorted by cost, snake deal).
+//   phase 1 : every warp walks its own list; 16 pixels per lane, rows in blocks of four
+//             from two exponentials per column, next record and next coefficients
+//             requested one step ahead.
+//   zoom    : margin -> tap table -> H pass in place (column taps in registers) -> halo
+//             row exchange -> ONE V pass whose results stay in registers -> arg-max ->
+//             scaled 128-bit stores, half of the band through a staged bulk copy that
+//             drains under the next image.  The float64 peak for the labels is evaluated
+//             by warp 1 (first CTA) while the others already render the next image.
 #include <cooperative_groups.h>
 
 #include "jet_common.cuh"
