@@ -17,20 +17,28 @@ from .packer import JetBatch, pack_jets, source_lists
 __all__ = ["apply_train_type", "component_from_list", "create_jet", "render_batch"]
 
 
-def render_batch(batch: JetBatch, normalize: bool, planes: bool = False, f64: bool = True, planes_out=None):
+def render_batch(batch: JetBatch, normalize: bool, planes: bool = False, f64: bool = True, planes_out=None,
+                 out=None):
     """Render a packed batch on the current device through the host-buffer C ABI.
 
     Returns ``(images[n, N, N], margin[n] int32, peak[n] float64, planes or None)``.
     ``planes_out``: a host array ``[n, P >= slots, N, N]`` of the output dtype (best page-locked)
     whose first ``slots`` planes per image receive the component planes directly.
+    ``out``: ``(images, margin, peak)`` host arrays (contiguous, of the right dtypes) to fill
+    instead of fresh ones -- slices of a larger page-locked block when a call is pipelined.
     """
     L.require_device()
     n, size, slots = batch.n, batch.size, batch.slots
     flags = (L.JET_NORMALIZE if normalize else 0) | (L.JET_OUT_F64 if f64 else 0)
     dt = np.float64 if f64 else np.float32
-    img = L.pinned_empty((n, size, size), dt)
-    margin = L.pinned_empty((n,), np.int32)
-    peak = L.pinned_empty((n,), np.float64)
+    if out is None:
+        img = L.pinned_empty((n, size, size), dt)
+        margin = L.pinned_empty((n,), np.int32)
+        peak = L.pinned_empty((n,), np.float64)
+    else:
+        img, margin, peak = out
+        assert img.shape == (n, size, size) and img.dtype == dt and img.flags.c_contiguous
+        assert margin.dtype == np.int32 and peak.dtype == np.float64 and len(margin) == len(peak) == n
     p = np.ascontiguousarray(batch.params, dtype=np.float64)
     zp = np.ascontiguousarray(batch.zoom_pad, dtype=np.int32)
     if n:
@@ -81,6 +89,36 @@ def apply_train_type(train_type, jet_img, jet_comp, source_list):
     raise UnboundLocalError(f"unknown training type {train_type!r}")
 
 
+_PIPE_CHUNK = 512
+
+
+def _pack_and_render_pipelined(n, size, comps, scaling, normalize):
+    """Large batches: the RNG chain of chunk i+1 is drawn on a helper thread while chunk i is
+    rendered and copied back (both release the GIL).  The chunks are packed strictly one after the
+    other, so the global ``np.random`` stream is consumed exactly as by one ``pack_jets(n, ...)``."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    img = L.pinned_empty((n, size, size), np.float64)
+    margin = L.pinned_empty((n,), np.int32)
+    peak = L.pinned_empty((n,), np.float64)
+    parts = []
+    with ThreadPoolExecutor(1) as ex:
+        fut = ex.submit(pack_jets, min(_PIPE_CHUNK, n), size, comps, scaling)
+        i0 = 0
+        while i0 < n:
+            b = fut.result()
+            i1 = i0 + b.n
+            if i1 < n:
+                fut = ex.submit(pack_jets, min(_PIPE_CHUNK, n - i1), size, comps, scaling)
+            render_batch(b, normalize, out=(img[i0:i1], margin[i0:i1], peak[i0:i1]))
+            parts.append(b)
+            i0 = i1
+    batch = JetBatch(size, parts[0].slots, np.concatenate([b.params for b in parts]),
+                     np.concatenate([b.extra for b in parts]), np.concatenate([b.zoom_pad for b in parts]),
+                     np.concatenate([b.zoom_out for b in parts]))
+    return batch, img, np.asarray(margin), np.asarray(peak)
+
+
 def create_jet(grid, conf):
     """Drop-in for ``radiosim.jets.create_jet`` (``jets/jet.py:14-197``).
 
@@ -92,12 +130,15 @@ def create_jet(grid, conf):
     size = shape[-1]
     scaling = conf.jet.scaling
     ttype = conf.jet.training_type
-    batch = pack_jets(n, size, conf.jet.num_jet_components, scaling)
     normalize = scaling == "normalize"
     gauss_targets = None
-    if ttype == "gauss":  # planes, background and list plane side by side: the planes land there directly
-        gauss_targets = L.pinned_empty((n, batch.slots + 2, size, size), np.float64)
-    img, margin, peak, planes = render_batch(batch, normalize, planes=(ttype == "gauss"), planes_out=gauss_targets)
+    if ttype != "gauss" and n >= 2 * _PIPE_CHUNK:
+        batch, img, margin, peak = _pack_and_render_pipelined(n, size, conf.jet.num_jet_components, scaling, normalize)
+    else:
+        batch = pack_jets(n, size, conf.jet.num_jet_components, scaling)
+        if ttype == "gauss":  # planes, background and list plane side by side: the planes land there directly
+            gauss_targets = L.pinned_empty((n, batch.slots + 2, size, size), np.float64)
+        img, margin, peak, _ = render_batch(batch, normalize, planes=(ttype == "gauss"), planes_out=gauss_targets)
     slist = source_lists(batch, margin, peak, normalize)
     jets = img[:, None, :, :]  # (page-locked block owned by the array; recycled when it is released)
     if ttype == "list":

@@ -154,3 +154,23 @@ def test_full_size_properties():
     # determinism
     img2, margin2, peak2, _ = render_batch(b, True, f64=False)
     assert np.array_equal(img, img2) and np.array_equal(margin, margin2) and np.array_equal(peak, peak2)
+
+
+def test_pipelined_create_jet_equals_single_shot():
+    """Large batches are packed in chunks on a helper thread while the previous chunk renders:
+    same stream consumption, same images, same targets as one pack + one render."""
+    from radiosim_b200.jets import create_jet
+    from radiosim_b200.jets.jet import _PIPE_CHUNK, render_batch
+    from radiosim_b200.jets.packer import pack_jets, source_lists
+
+    n, size = 2 * _PIPE_CHUNK + 77, 64
+    np.random.seed(99)
+    x, y = create_jet(_grid(n, size), _conf("list"))
+    end_a = np.random.rand()
+    np.random.seed(99)
+    b = pack_jets(n, size, (3, 10), "normalize")
+    end_b = np.random.rand()
+    img, margin, peak, _ = render_batch(b, True)
+    assert end_a == end_b
+    assert x.shape == (n, 1, size, size) and np.array_equal(x[:, 0], img)
+    assert np.array_equal(y, source_lists(b, margin, peak, True))
