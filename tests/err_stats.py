@@ -9,11 +9,12 @@ from radiosim_b200.jets.packer import pack_jets
 worst = 0.0
 import os
 SCALE = int(os.environ.get("RSB_ERR_SCALE", "1"))  # more jets per case
+COMPS = tuple(int(v) for v in os.environ.get("RSB_ERR_COMPS", "3,10").split(","))  # num_jet_components
 for size, n, seed in [(128, 48, 1), (200, 32, 2), (256, 64, 3), (256, 64, 11), (64, 48, 5)]:
     n *= SCALE
     np.random.seed(seed); tr = []
-    ox, _ = ojet.create_jet((n, 3, size, size), (3, 10), "normalize", "clean", trace=tr)
-    np.random.seed(seed); b = pack_jets(n, size, (3, 10), "normalize")
+    ox, _ = ojet.create_jet((n, 3, size, size), COMPS, "normalize", "clean", trace=tr)
+    np.random.seed(seed); b = pack_jets(n, size, COMPS, "normalize")
     img, margin, peak, _ = render_batch(b, True, f64=False)
     e = np.abs(img - ox[:, 0]).reshape(n, -1).max(axis=1)
     pk = np.array([t["jet_max"] for t in tr]); mg = np.array([t["margin"] for t in tr])
