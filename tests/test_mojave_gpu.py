@@ -60,3 +60,58 @@ def test_create_mojave_bundle_matches_reference_golden(golden_dir):
     with pytest.raises(ValueError):
         conf.general.threads = -2
         create_mojave(conf, np.random.default_rng(0))
+
+
+# ---- the warps of the kernel against what is known of scikit-image from outside -------------
+# (scikit-image exists neither in the build container nor on the GPU box; see
+# tests/test_warps_cpu.py for the sources of these facts)
+def _one_gauss_source(size, g, angle, jet=None, strength=0.0, radius=100.0):
+    from radiosim_b200.mojave import mojave as mm
+
+    s = mm._Source(size)
+    if g is not None:
+        s.gauss.append(list(g))
+    if jet is not None:
+        j = mm._base_jet(size, *jet)
+        j.strength, j.radius = strength, radius
+        s.jets = [j]
+    s.angle = angle
+    return s
+
+
+@pytest.mark.parametrize("size", [64, 97])
+def test_kernel_rotate_quarter_turns_equal_rot90(size):
+    """skimage's own known answer (rotate(x, 90) == np.rot90(x)): direction and the
+    (N/2 - 0.5) centre.  A quarter turn maps pixels onto pixels, so the match is to float32
+    rounding of the same values."""
+    from radiosim_b200.mojave.mojave import render_sources
+
+    g = [1.0, size / 2 + 11.3, size / 2 - 6.7, 5.0, 2.5, 0.4]
+    imgs = render_sources([_one_gauss_source(size, g, 90.0 * k) for k in range(4)], size)
+    base = imgs[0]
+    assert base.max() > 0.9
+    for k in range(1, 4):
+        assert np.abs(imgs[k] - np.rot90(base, k)).max() <= 1e-6, k
+
+
+def test_kernel_swirl_identity_and_direction():
+    from radiosim_b200.mojave.mojave import gen_jet, render_sources
+
+    size = 128
+    jet = (1.0, 4.0, 25.0, 4)   # amplitude, width, length, skew: extends to the right of the centre
+    plain = gen_jet(size, *jet)
+    # strength 0 -> the swirl is the identity (up to the bilinear taps at integer positions)
+    same = render_sources([_one_gauss_source(size, None, 0.0, jet, 0.0, 120.0)], size)[0]
+    assert np.abs(same - plain).max() <= 1e-6
+    # reverse map theta' = theta + s*exp(-rho/r): the content moves by -s*exp(-rho/r) in atan2(row, col)
+    s, radius = 0.5, 150.0
+    sw = render_sources([_one_gauss_source(size, None, 0.0, jet, s, radius)], size)[0]
+    yy, xx = np.mgrid[0:size, 0:size]
+    sel = (xx - size / 2) > 20    # the part of the jet well away from the centre
+    def ang(img):
+        w = img * sel
+        return np.arctan2((w * (yy - size / 2)).sum(), (w * (xx - size / 2)).sum())
+    rho = 30.0
+    expect = -s * np.exp(-rho / (radius / 5 * np.log(2)))
+    assert ang(plain) == pytest.approx(0.0, abs=2e-2)
+    assert ang(sw) < -0.1 and ang(sw) == pytest.approx(expect, abs=0.12)

@@ -48,6 +48,29 @@ def test_survey_matches_oracle(size, n, ns, seed, dist):
     assert np.abs(x.reshape(n, -1).max(axis=1) - 1.0).max() <= 2e-6
 
 
+@pytest.mark.parametrize("ns,dist,seed", [
+    (2000, (2, 1, 2), 1337),   # BASELINE config 4 as SURVEY 8d words it: ~800 sub-jets of 100..199 px
+    (5000, (0, 1, 2), 1338),   # no sub-jets: >= 10 staged chunks of records in a tile, float32 sums of
+])                             # thousands of terms, the footprint cut at its worst
+def test_survey_config4_source_counts_match_oracle(ns, dist, seed):
+    """One 1024^2 image with the source counts BASELINE config 4 names, against the float64
+    oracle (threads only split its sum over sources)."""
+    from oracle import survey as osur
+    from radiosim_b200.survey import create_survey
+
+    size = 1024
+    np.random.seed(seed)
+    ox, oy = osur.create_survey((1, 3, size, size), ns, dist, True, workers=os.cpu_count() or 1)
+    o_next = np.random.rand()
+    np.random.seed(seed)
+    x, y = create_survey(np.broadcast_to(np.zeros(1), (1, 3, size, size)), _conf(ns, dist))
+    assert np.random.rand() == o_next  # RNG stream aligned after thousands of draws
+    ex, ey = np.abs(x - ox).max(), np.abs(y - oy).max()
+    print(f"survey 1024^2, {ns} sources {dist}: max abs err x {ex:.3e}, y {ey:.3e} (of peak 1)")
+    assert ex <= TOL and ey <= TOL
+    assert abs(float(x.max()) - 1.0) <= 2e-6
+
+
 def test_survey_large_grid_properties():
     """BASELINE config 4 size (1024^2, thousands of sources): oracle-free properties."""
     from radiosim_b200.survey.survey import pack_survey, render_survey

@@ -8,7 +8,9 @@ shared memory, e.g. 384x384) is replaced by a 32 MiB array built into the librar
 
 The test drives both entry points through the C ABI on the same inputs, twice in a
 row with different batches (the shared array keeps the first call's contents, which
-must not leak into the second), and asks for the same images, margins and peaks.
+must not leak into the second), and asks for the same images, margins and peaks.  The
+static entry is also held against the float64 oracle directly (images within 1e-5 of the
+peak, margins exact), so the check does not rest on the other CUDA entry point alone.
 It is collected last on purpose: a run that stops at the first failure has already
 run every other test.
 """
@@ -65,6 +67,26 @@ def test_static_scratch_entry_matches_workspace_entry():
         assert np.allclose(k, ref_k, rtol=1e-6, atol=0), f"call {call}"
         # the tolerance of the other jet tests: 1e-5 of the (normalised) image peak
         assert np.abs(img - ref_img).max() <= 1e-5, f"call {call}"
+
+
+def test_static_scratch_entry_matches_oracle():
+    """384x384 jets through the no-allocation entry against ``oracle.jet`` (float64)."""
+    from oracle import jet as ojet
+    from radiosim_b200 import _lib as L
+    from radiosim_b200.jets.packer import pack_jets
+
+    L.require_device()
+    n = 12
+    np.random.seed(303)
+    trace = []
+    ox, _ = ojet.create_jet((n, 3, SIZE, SIZE), (3, 10), "normalize", "clean", trace=trace)
+    np.random.seed(303)
+    b = pack_jets(n, SIZE, (3, 10), "normalize")
+    for call in range(2):
+        img, m, k = _render(L, "rsb_jet_render_static", b.params, b.zoom_pad, False)
+        assert np.array_equal(m, np.array([t["margin"] for t in trace])), f"call {call}"
+        assert np.allclose(k, np.array([t["jet_max"] for t in trace]), rtol=1e-6, atol=0), f"call {call}"
+        assert np.abs(img.astype(np.float64) - ox[:, 0]).max() <= 1e-5, f"call {call}"
 
 
 def test_static_scratch_entry_rejects_oversize():
