@@ -12,8 +12,12 @@ the ones the reference writes (``src/radiosim/utils/utils.py:344-383``,
 * scalar variable-length UTF-8 strings (ppdisk ``metadata`` / ``params``), stored
   through a global heap collection (``GCOL``).
 
-Files written here open in h5py / ``h5dump``; files h5py wrote with default
-settings (e.g. the reference fixture ``tests/ppdisks_128.h5``) read back here.
+The writer lays a file out the way libhdf5 does for h5py's defaults: writing the reference
+fixture's dataset back gives the fixture **byte for byte** (``tests/test_h5_format.py``), and
+every written structure is walked by an independent checker of the format specification in
+the same test module.  No HDF5 library exists in the build container or on the GPU box, so
+"opens in h5py" itself could not be run.  Files h5py wrote with default settings (e.g. the
+reference fixture ``tests/ppdisks_128.h5``) read back here.
 """
 
 from __future__ import annotations
@@ -57,8 +61,10 @@ def _dtype_message(dt: np.dtype) -> bytes:
 
 
 def _vlen_str_dtype_message() -> bytes:
-    # class 9 vlen, type=string(1), pad null-term(0), cset utf8(1); base = 1-byte string
-    base = struct.pack("<BBBBI", 0x13, 0x10, 0, 0, 1)
+    # class 9 vlen, type=string(1), pad null-term(0), cset utf8(1).  The parent type libhdf5
+    # stores for a variable-length string is a 1-byte unsigned integer (H5T__set_size copies
+    # H5T_NATIVE_UCHAR): class 0, little-endian, unsigned, offset 0, precision 8
+    base = struct.pack("<BBBBI", 0x10, 0x00, 0, 0, 1) + struct.pack("<HH", 0, 8)
     return struct.pack("<BBBBI", 0x19, 0x01, 0x01, 0, 16) + base
 
 
@@ -87,28 +93,30 @@ def write_h5(path, datasets: dict) -> None:
     names = sorted(datasets)
     if len(names) > 8:
         raise ValueError("h5min writes at most 8 datasets per file")
-    # ---- local heap data: "" at 0, then names
+    # ---- local heap data: "" at 0, then names.  libhdf5 sizes a fresh group's heap for four
+    # 8-character names (8 + 4 * 16 + 16 = 88 bytes, H5G__obj_create's default hint); keep that
+    # size when the names fit, so that small files have the layout h5py gives them.
     heap = bytearray(b"\x00" * 8)
     name_off = {}
     for n in names:
         name_off[n] = len(heap)
         enc = n.encode() + b"\x00"
         heap += enc + b"\x00" * (_pad8(len(enc)) - len(enc))
-    heap_data_size = _pad8(len(heap) + 16)
+    heap_data_size = max(88, _pad8(len(heap) + 16))
     free_off = len(heap)
     heap += b"\x00" * (heap_data_size - len(heap))
     struct.pack_into("<QQ", heap, free_off, 1, heap_data_size - free_off)
 
-    # ---- fixed layout of the metadata block
+    # ---- fixed layout of the metadata block, in the order libhdf5 allocates it: root header,
+    # B-tree node, local heap, [first dataset's object header], symbol node, [other headers]
     off_root_hdr = 0x60
     root_hdr_len = 16 + 8 + 16
     off_tree = _pad8(off_root_hdr + root_hdr_len)
     tree_len = 24 + 8 * (2 * 16 + 1) + 8 * (2 * 16)
     off_heap = off_tree + tree_len
     off_heap_data = off_heap + 32
-    off_snod = off_heap_data + heap_data_size
     snod_len = 8 + 8 * 40
-    cursor = off_snod + snod_len
+    cursor = off_heap_data + heap_data_size
 
     # ---- datasets: object headers then raw data
     headers, raws, gcols = {}, {}, {}
@@ -128,15 +136,24 @@ def write_h5(path, datasets: dict) -> None:
             raws[n] = memoryview(a.reshape(-1).view(np.uint8)) if a.size else b""  # no copy: written straight from the array
     hdr_off, data_off, gcol_off = {}, {}, {}
     hdr_len = {}
+    off_snod = None
     for n in names:
         kind, shape, dt = headers[n]
         hdr_off[n] = cursor
         rank = len(shape)
         ds_len = 8 + _pad8(8 + 16 * rank)
         dt_body = _vlen_str_dtype_message() if kind == "vlen" else _dtype_message(dt)
-        hl = 16 + ds_len + 8 + _pad8(len(dt_body)) + 8 + 8 + 8 + 24
-        hdr_len[n] = hl
-        cursor = _pad8(cursor + hl)
+        used = ds_len + 8 + _pad8(len(dt_body)) + 8 + 8 + 8 + 24
+        # libhdf5 gives a dataset's header 256 bytes of message space (H5D_MINHDR_SIZE) and
+        # fills what is left with one NIL message
+        hdr_len[n] = 16 + (256 if used + 8 <= 256 or used == 256 else used)
+        cursor = _pad8(cursor + hdr_len[n])
+        if off_snod is None:  # the symbol node is created when the first link is inserted
+            off_snod = cursor
+            cursor += snod_len
+    if off_snod is None:
+        off_snod = cursor
+        cursor += snod_len
     cursor = (cursor + 0x7FF) & ~0x7FF if cursor <= 0x800 else _pad8(cursor)
     head_len = cursor  # superblock, group structures and object headers; the data follows
     for n in names:
@@ -191,8 +208,11 @@ def write_h5(path, datasets: dict) -> None:
             _message(0x05, struct.pack("<BBBBI", 2, 2, 2, 1, 0), flags=1),  # fill value: size 0
             _message(0x08, struct.pack("<BBQQ", 3, 1, data_off[n], nbytes)),
         ]
+        room = hdr_len[n] - 16 - sum(len(m) for m in msgs)
+        if room >= 8:
+            msgs.append(_message(0x00, b"\x00" * (room - 8)))  # NIL: the rest of the header block
         hdr = _object_header(msgs)
-        assert len(hdr) <= hdr_len[n], (len(hdr), hdr_len[n])
+        assert len(hdr) == hdr_len[n], (len(hdr), hdr_len[n])
         out[hdr_off[n] : hdr_off[n] + len(hdr)] = hdr
         if kind == "vlen":
             g = gcol_off[n]
