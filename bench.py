@@ -3,22 +3,27 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-One "step" = one pass of the jet hot path (splat -> zoom -> normalise) over one
-batch of pre-packed jets per GPU.  Parameters come from the reference's own RNG
-chain (radiosim_b200.jets.packer, per-rank seed 1337+rank), so the live-component
-count, widths and the ~70 % zoom rate are the reference's.
+One "step" = one SWEEP of the jet hot path (splat -> zoom -> normalise) over 1 000 000
+pre-packed jets per GPU, rendered in chunks of 16 384 images into a 4 GiB float32 ring
+buffer in HBM (62 launches).  Parameters come from the
+reference's own RNG chain (radiosim_b200.jets.packer, per-rank seed 1337+rank), so the
+live-component count, widths and the ~70 % zoom rate are the reference's.
 
-* ``value``  -- device-resident parameters, float32 images written to an HBM ring
-  buffer (batch x 256 KiB >> L2), CUDA events on the launching stream, max over ranks.
-* ``e2e``    -- same metric through the host-buffer C-ABI call
-  (``rsb_jet_render_host``): pinned host parameters in, pinned host images out,
-  copies inside the timed region.
-* ``roofline`` -- HBM view (algorithmic bytes / launch time vs the measured copy
-  bandwidth) plus the governing SFU view (``sfu_*``: algorithmic exp count vs the
-  MUFU.EX2 rate measured on this very device).
-* ``cpu_baseline`` / ``--impl reference`` -- the reference's CPU algorithm (numpy
-  restatement in ``oracle/``; /root/reference does not exist on the GPU box) on the
-  host cores, one process per core.
+* ``value``  -- device-resident parameters, CUDA events on the launching stream, max over
+  ranks, whole-box images/s.
+* ``e2e``    -- same metric through the host-buffer C-ABI call (``rsb_jet_render_host``):
+  pinned host parameters in, pinned host float32 images out, copies inside the timed region.
+  ``e2e_dropin`` is the reference-facing Python call itself, ``create_jet(grid, conf)``: RNG
+  chain drawn, float64 host arrays returned.
+* ``roofline`` -- HBM view (algorithmic bytes / launch time vs the measured copy bandwidth)
+  plus the governing SFU view (``sfu_*``: algorithmic and executed exp counts vs the MUFU.EX2
+  rate measured on this very device).  DRAM traffic and executed-instruction counts come from
+  the committed ncu capture of this build (``profiles/ncu_summary.json``).
+* ``configs`` -- the other BASELINE.json configurations (C2 mojave, C3 ppdisk, C4 survey):
+  device-timed images/s, end to end through the drop-in, and a roofline object each.
+* ``cpu_baseline`` / ``--impl reference`` -- the reference's CPU algorithm (numpy restatement
+  in ``oracle/``; /root/reference does not exist on the GPU box) on the host cores, one
+  process per core.
 """
 
 from __future__ import annotations
@@ -40,10 +45,24 @@ sys.path.insert(0, ROOT)
 SIZE = 256
 COMPS = (3, 10)
 SLOTS = 2 * COMPS[1] - 1
+SWEEP = 1_000_000       # images per GPU per step
+CHUNK = 16_384          # images per launch
 METRIC = "images/sec (whole box) for 256x256 jet batches"
 UNIT = "images/s"
-NCU_DRAM_BYTES_PER_IMAGE = 248657  # measured, see profiles/README.md
 WORKLOAD = "C5: jet 256x256, default jet params (num_jet_components [3,10], scaling normalize)"
+
+
+def shared_config(world):
+    """The same dictionary in both arms (the driver compares them)."""
+    return {
+        "workload": WORKLOAD, "img_size": SIZE, "slots": SLOTS, "num_jet_components": list(COMPS),
+        "scaling": "normalize", "seed": "1337+rank (CUDA arm) / 4242+process (reference arm)",
+        "parallelism": f"dp{world} (independent shards, no collective)",
+        "sweep": f"CUDA arm: {SWEEP} images per GPU per step in launches of {CHUNK}; "
+                 "reference arm: a bounded sample of the same workload per step",
+        "l2_policy": f"every launch writes {CHUNK * SIZE * SIZE * 4 / 2**20:.0f} MiB of images "
+                     "(ring buffer in HBM) >> 126 MB L2",
+    }
 
 
 # ----------------------------------------------------------------------------- utils
@@ -92,8 +111,8 @@ class ClockSampler:
                 self.proc.kill()
 
     def summary(self, t0, t1):
-        inwin = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.15] or [r for (_, r) in self.rows]
-        sm, smax, reasons = [], [], set()
+        inwin = [r for (t, r) in self.rows if t0 <= t <= t1]
+        sm, smax, power, reasons = [], [], [], set()
         for r in inwin:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 9:
@@ -101,6 +120,7 @@ class ClockSampler:
             try:
                 sm.append(float(f[1]))
                 smax.append(float(f[2]))
+                power.append(float(f[3]))
             except ValueError:
                 continue
             for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
@@ -109,8 +129,8 @@ class ClockSampler:
                     reasons.add(name)
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)),
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_mhz_min": float(min(sm)), "sm_max_mhz": float(max(smax)),
+                "power_w_max": float(max(power)), "reasons": sorted(reasons), "samples": len(sm)}
 
 
 def measured_peaks():
@@ -124,6 +144,14 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_summary():
+    """Per-unit DRAM traffic / executed-instruction counts of the committed ncu captures."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
+    except Exception:
+        return {}
+
+
 # ------------------------------------------------------------------- CPU reference arm
 def _cpu_worker(args):
     seed, n = args
@@ -135,16 +163,26 @@ def _cpu_worker(args):
     return time.perf_counter() - t
 
 
-def cpu_reference_rate(images_per_proc: int, procs: int, seed0: int = 4242):
-    """images/s of the reference algorithm (oracle port), one process per core."""
-    import multiprocessing as mp
+class CpuPool:
+    """One process per host core, kept alive across steps and warmed (imports, page faults)
+    before anything is timed -- both CPU figures of a box come from this one sampler."""
 
-    ctx = mp.get_context("fork")
-    t = time.perf_counter()
-    with ctx.Pool(procs) as pool:
-        pool.map(_cpu_worker, [(seed0 + i, images_per_proc) for i in range(procs)])
-    dt = time.perf_counter() - t
-    return images_per_proc * procs / dt, dt
+    def __init__(self, procs):
+        import multiprocessing as mp
+
+        self.procs = procs
+        self.pool = mp.get_context("fork").Pool(procs)
+        self.pool.map(_cpu_worker, [(7 + i, 2) for i in range(procs)])
+
+    def rate(self, images_per_proc, seed0=4242):
+        t = time.perf_counter()
+        self.pool.map(_cpu_worker, [(seed0 + i, images_per_proc) for i in range(self.procs)], chunksize=1)
+        dt = time.perf_counter() - t
+        return images_per_proc * self.procs / dt, dt
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
 
 
 def run_reference(args):
@@ -152,22 +190,25 @@ def run_reference(args):
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    # bounded sample: ~28 ms per 256x256 jet per core; keep the whole run near 2 minutes
-    per = max(4, min(200, int(120.0 / max(args.steps, 1) / 0.030)))
+    # bounded sample: ~25-30 ms per 256x256 jet per core; keep the whole run near 2 minutes
+    per = max(100, min(200, int(120.0 / max(args.steps, 1) / 0.030)))
+    pool = CpuPool(cores)
     for _ in range(min(args.warmup, 1)):
-        cpu_reference_rate(4, cores)
+        pool.rate(8)
     t_tot, n_tot = 0.0, 0
-    for _ in range(args.steps):
-        rate, dt = cpu_reference_rate(per, cores)
+    for s in range(args.steps):
+        rate, dt = pool.rate(per, 4242 + 1000 * s)
         t_tot += dt
         n_tot += per * cores
+    pool.close()
     value = n_tot / t_tot
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_tot / max(args.steps, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch_per_step": per * cores,
+        "config": shared_config(args.gpus),
+        "sample": {"images_per_step": per * cores,
                    "note": "reference CPU algorithm (numpy port in oracle/), host cores only"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{per} images x {cores} processes per step"},
@@ -178,16 +219,169 @@ def run_reference(args):
     return 0
 
 
+# ------------------------------------------------------------- other configs (C2-C4)
+class _Events:
+    def __init__(self, L):
+        self.L, self.lib = L, L.lib()
+        self.ev = [C.c_void_p(), C.c_void_p()]
+        for e in self.ev:
+            L.check(self.lib.rsb_event_create(C.byref(e)))
+
+    def time(self, fn, reps, warm=2):
+        """Average milliseconds of ``fn`` (enqueues on the default stream), CUDA events."""
+        for _ in range(warm):
+            fn()
+        self.L.device_sync()
+        self.L.check(self.lib.rsb_event_record(self.ev[0], None))
+        for _ in range(reps):
+            fn()
+        self.L.check(self.lib.rsb_event_record(self.ev[1], None))
+        ms = C.c_float()
+        self.L.check(self.lib.rsb_event_elapsed_ms(self.ev[0], self.ev[1], C.byref(ms)))
+        return ms.value / reps
+
+
+def _wall(fn, reps, warm=1):
+    for _ in range(warm):
+        fn()
+    t = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    return (time.perf_counter() - t) / reps
+
+
+def bench_survey(L, ev, hbm_peak, sfu_peak, prof, ns, n=4, size=1024):
+    """C4: survey 1024^2, ``ns`` sources per image, class_distribution [2,1,2]."""
+    from types import SimpleNamespace as NS
+
+    from radiosim_b200.survey import survey as sv
+
+    lib = L.lib()
+    conf = NS(jet=NS(training_type="list", scaling="normalize", num_jet_components=list(COMPS)),
+              survey=NS(num_sources=ns, class_distribution=[2, 1, 2], scale_sources=True))
+    np.random.seed(1337)
+    b = sv.pack_survey(n, size, ns, (2, 1, 2), True)
+    dev = sv.DeviceSurvey(b, jet_normalize=True, f64=False)
+    launches0 = L.launch_count()
+    ms = ev.time(dev.enqueue, reps=5)
+    launches = (L.launch_count() - launches0) // 7
+    grid = np.broadcast_to(np.zeros(1), (n, 3, size, size))
+
+    def dropin():
+        np.random.seed(1337)
+        sv.create_survey(grid, conf)
+
+    wall = _wall(dropin, reps=2)
+    total = b.src_params.shape[0]
+    bytes_img = 4 * size * size * 5
+    rate = n / (ms * 1e-3)
+    p = prof.get("survey_tile", {})
+    out = {
+        "config": f"C4: survey {size}x{size}, {ns} sources per image, class_distribution [2,1,2]",
+        "images": n, "value": rate, "unit": UNIT, "ms_per_image": ms / n,
+        "gpu_launches_per_batch": launches, "sub_jets_per_image": b.njets / n,
+        "gaussians_per_image": total / n,
+        "e2e": {"value": n / wall, "unit": UNIT, "call": "create_survey(grid, conf): RNG chain, float64 host arrays",
+                "d2h_bytes_per_image": 8 * size * size * 5},
+        "roofline": {"bound": "hbm", "achieved": rate * bytes_img / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": rate * bytes_img / 1e9 / hbm_peak, "algorithmic_bytes_per_image": bytes_img,
+                     "traffic": p.get("dram_bytes_per_image"),
+                     "reference_ex2_per_image": (total / n) * size * size,
+                     "executed_ex2_per_image": p.get(f"executed_ex2_per_image_{ns}"),
+                     "sfu_peak_ex2_per_s": sfu_peak},
+    }
+    ex = out["roofline"]["executed_ex2_per_image"]
+    if ex:
+        out["roofline"]["sfu_executed_frac"] = rate * ex / sfu_peak
+    return out
+
+
+def bench_mojave(L, ev, hbm_peak, n=10_000, size=256):
+    """C2: mojave-like sources 256^2, 10 k images (bundle_size 1000 x 10 bundles), class_ratio [1,1,1]."""
+    from types import SimpleNamespace as NS
+
+    from radiosim_b200.mojave import mojave as mj
+
+    lib = L.lib()
+    conf = NS(general=NS(threads=None, seed=1337), dataset=NS(bundle_size=1000, img_size=size),
+              mojave=NS(class_ratio=[1, 1, 1]))
+    rng = np.random.default_rng(1337)
+    t = time.perf_counter()
+    rec, blobs, profs = mj.make_recipes(rng, mj.class_counts([1, 1, 1], 1000), size, 1)
+    recipe_s = time.perf_counter() - t
+    need = C.c_size_t(0)
+    L.check(lib.rsb_mojave_workspace_bytes(1000, size, C.byref(need)))
+    d_r, d_b, d_p = L.dev_from(rec), L.dev_from(blobs), L.dev_from(profs)
+    d_w, d_o = L.DeviceBuffer(need.value), L.DeviceBuffer(1000 * size * size * 4)
+
+    def enqueue():  # one bundle of 1000
+        L.check(lib.rsb_mojave_render(d_r.ptr, 1000, d_b.ptr, d_p.ptr, size, 0, d_o.ptr, d_w.ptr,
+                                      d_w.nbytes, None))
+
+    ms = ev.time(enqueue, reps=n // 1000)
+    state = {"k": 0}
+
+    def dropin():
+        state["k"] += 1
+        mj.create_mojave(conf, np.random.default_rng(1337 + state["k"]), today="2026-01-01")
+
+    wall = _wall(dropin, reps=3)
+    rate = 1000 / (ms * 1e-3)
+    bytes_img = 4 * size * size
+    return {
+        "config": f"C2: mojave {size}x{size}, {n} images (10 bundles of 1000), class_ratio [1,1,1]",
+        "images": n, "value": rate, "unit": UNIT, "ms_per_image": ms / 1000,
+        "host_recipe_images_per_s": 1000 / recipe_s,
+        "e2e": {"value": 1000 / wall, "unit": UNIT,
+                "call": "create_mojave(conf, rng), bundle_size 1000: child-generator recipes on the host, "
+                        "float64 host arrays", "d2h_bytes_per_image": 8 * size * size},
+        "roofline": {"bound": "hbm", "achieved": rate * bytes_img / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": rate * bytes_img / 1e9 / hbm_peak, "algorithmic_bytes_per_image": bytes_img,
+                     "traffic": None,
+                     "note": "three passes (evaluate, rotate, recentre) through global scratch; "
+                             "float64 warp coordinates"},
+    }
+
+
+def bench_ppdisk(L, ev, hbm_peak, n=50, size=512):
+    """C3: ppdisk 512^2 with the ranges of rc/default_ppdisks_simulation.toml (batch_size 5 x 10)."""
+    from radiosim_b200.ppdisks import ppdisks as pp
+
+    np.random.seed(1337)
+    packed = []
+    for _ in range(n):
+        a = np.random.randint(0, 180)
+        r = np.random.randint(3, 15) / np.random.randint(3, 15)
+        packed.append(pp.pack_proto(size, a, r, np.random.uniform(0.1, 1)))
+    dev = pp.DeviceProtos(size, packed)
+    ms = ev.time(dev.enqueue, reps=5)
+
+    def dropin():
+        pp.generate_proto_set(size, n, (0, 180), (3, 15), (0.1, 1.0), "cuda", 1337, False)
+
+    wall = _wall(dropin, reps=3)
+    rate = n / (ms * 1e-3)
+    bytes_img = 4 * size * size
+    return {
+        "config": f"C3: ppdisk {size}x{size}, default ppdisk TOML ranges, {n} images",
+        "images": n, "value": rate, "unit": UNIT, "ms_per_image": ms / n,
+        "e2e": {"value": n / wall, "unit": UNIT,
+                "call": "generate_proto_set(512, 50, ...): RNG chain, float32 host arrays",
+                "d2h_bytes_per_image": 4 * size * size},
+        "roofline": {"bound": "hbm", "achieved": rate * bytes_img / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": rate * bytes_img / 1e9 / hbm_peak, "algorithmic_bytes_per_image": bytes_img,
+                     "traffic": None,
+                     "note": "work is the 900x900 mask + separable blur per component (L2/FP32), "
+                             "not the 1 MB image written"},
+    }
+
+
 # ------------------------------------------------------------------------- CUDA arm
 def run_cuda(args):
     rank, world = env_int("RANK", 0), env_int("WORLD_SIZE", 1)
     local = env_int("LOCAL_RANK", 0)
     dist = None
-    near = []
     if world > 1:
-        from radiosim_b200.sharder import bind_near_gpu
-
-        near = bind_near_gpu(local)  # host buffers on the GPU's own socket (matters for the e2e leg)
         import torch
         import torch.distributed as dist_mod
 
@@ -202,33 +396,36 @@ def run_cuda(args):
     L.set_device(local)
     lib = L.lib()
 
-    batch = args.batch
+    sweep, chunk = args.sweep, min(args.batch, args.sweep)
     np.random.seed(1337 + rank)
     t_pack = time.perf_counter()
-    jb = pack_jets(batch, SIZE, COMPS, "normalize")
-    pack_rate = batch / (time.perf_counter() - t_pack)
+    jb = pack_jets(sweep, SIZE, COMPS, "normalize")
+    pack_rate = sweep / (time.perf_counter() - t_pack)
     live = int((jb.params[:, :, 0] != 0).sum())
     zoom_frac = float((jb.zoom_pad >= 0).mean())
 
     flags = L.JET_NORMALIZE
     d_params = L.dev_from(jb.params)
     d_pad = L.dev_from(jb.zoom_pad)
-    d_img = L.DeviceBuffer(batch * SIZE * SIZE * 4)
-    d_margin = L.DeviceBuffer(batch * 4)
-    d_peak = L.DeviceBuffer(batch * 8)
+    d_img = L.DeviceBuffer(chunk * SIZE * SIZE * 4)          # the ring: every launch overwrites it
+    d_margin = L.DeviceBuffer(sweep * 4)
+    d_peak = L.DeviceBuffer(sweep * 8)
     wsz = C.c_size_t(0)
-    L.check(lib.rsb_jet_workspace_bytes(batch, SLOTS, SIZE, C.byref(wsz)))
+    L.check(lib.rsb_jet_workspace_bytes(chunk, SLOTS, SIZE, C.byref(wsz)))
     d_work = L.DeviceBuffer(max(wsz.value, 16))
     stream = C.c_void_p()
     L.check(lib.rsb_stream_create(C.byref(stream)))
     ev = [C.c_void_p() for _ in range(2)]
     for e in ev:
         L.check(lib.rsb_event_create(C.byref(e)))
+    starts = list(range(0, sweep, chunk))
 
     def step():
-        L.check(lib.rsb_jet_render(d_params.ptr, d_pad.ptr, batch, SLOTS, SIZE, flags, d_img.ptr,
-                                   d_margin.ptr, d_peak.ptr, d_work.ptr, d_work.nbytes, stream),
-                "rsb_jet_render")
+        for i0 in starts:
+            cnt = min(chunk, sweep - i0)
+            L.check(lib.rsb_jet_render(d_params.ptr + i0 * SLOTS * 48, d_pad.ptr + i0 * 4, cnt, SLOTS, SIZE,
+                                       flags, d_img.ptr, d_margin.ptr + i0 * 4, d_peak.ptr + i0 * 8,
+                                       d_work.ptr, d_work.nbytes, stream), "rsb_jet_render")
 
     def barrier():
         L.check(lib.rsb_stream_sync(stream))
@@ -241,7 +438,8 @@ def run_cuda(args):
 
     sampler = ClockSampler(local)
     sampler.start()
-    for _ in range(max(args.warmup, 3)):
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
         step()
     barrier()
     launches0 = L.launch_count()
@@ -259,7 +457,7 @@ def run_cuda(args):
     elapsed_ms = float(ms.value)
 
     # ---- e2e: host-buffer C-ABI call, pinned buffers, copies inside the timed region
-    eb = min(args.e2e_batch, batch)
+    eb = min(args.e2e_batch, sweep)
     h_params = L.pinned_empty((eb, SLOTS, 6), np.float64)
     h_params[:] = jb.params[:eb]
     h_pad = L.pinned_empty((eb,), np.int32)
@@ -282,17 +480,40 @@ def run_cuda(args):
         e2e_step()
     L.device_sync()
     e2e_s = time.perf_counter() - te
-    sampler.stop()
-
     # sanity of the result actually read back
     assert abs(float(h_img[0].max()) - 1.0) < 1e-5 and np.isfinite(h_peak).all()
+    del h_img
+
+    # ---- e2e through the drop-in itself: create_jet(grid, conf) -- RNG chain + float64 host arrays
+    from types import SimpleNamespace as NS
+
+    from radiosim_b200.jets import create_jet
+
+    conf = NS(jet=NS(training_type="list", scaling="normalize", num_jet_components=list(COMPS)))
+    grid = np.broadcast_to(np.zeros(1), (eb, 3, SIZE, SIZE))
+    res = None
+    for _ in range(2):
+        res = None
+        np.random.seed(99 + rank)
+        res = create_jet(grid, conf)
+    barrier()
+    dropin_steps = 5
+    td = time.perf_counter()
+    for k in range(dropin_steps):
+        res = None   # release the previous result: its page-locked block is recycled
+        np.random.seed(100 + k + rank)
+        res = create_jet(grid, conf)
+    dropin_s = time.perf_counter() - td
+    assert res[0].dtype == np.float64 and res[0].shape == (eb, 1, SIZE, SIZE)
+    res = None
+    sampler.stop()
 
     if dist is not None:
         import torch
 
-        t = torch.tensor([elapsed_ms, e2e_s], device="cuda", dtype=torch.float64)
+        t = torch.tensor([elapsed_ms, e2e_s, dropin_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms, e2e_s = float(t[0]), float(t[1])
+        elapsed_ms, e2e_s, dropin_s = float(t[0]), float(t[1]), float(t[2])
         cnt = torch.tensor([float(live), float(launches)], device="cuda", dtype=torch.float64)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
         live_all, launches_all = float(cnt[0]), int(cnt[1])
@@ -300,59 +521,83 @@ def run_cuda(args):
         live_all, launches_all = float(live), launches
 
     if rank == 0:
-        value = world * batch * args.steps / (elapsed_ms * 1e-3)
+        value = world * sweep * args.steps / (elapsed_ms * 1e-3)
         e2e_value = world * eb * e2e_steps / e2e_s
         hbm_peak, peak_src = measured_peaks()
+        prof = ncu_summary()
+        pj = prof.get("jet2", {})
         # algorithmic traffic per image: one float32 image out + parameters in
         bytes_per_img = 4 * SIZE * SIZE + SLOTS * 6 * 8 + 4 + 4 + 8
-        per_gpu_rate = batch * args.steps / (elapsed_ms * 1e-3)
+        per_gpu_rate = sweep * args.steps / (elapsed_ms * 1e-3)
         achieved_gbs = per_gpu_rate * bytes_per_img / 1e9
-        exps_per_img = SIZE * SIZE * (live_all / (world * batch))
+        exps_per_img = SIZE * SIZE * (live_all / (world * sweep))
         sfu_achieved = per_gpu_rate * exps_per_img
+        n_launch = len(starts)
+        cfg = shared_config(world)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3),
+            "steps": args.steps, "warmup": warm,
             "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {
-                "workload": WORKLOAD, "batch_per_gpu": batch, "img_size": SIZE,
-                "slots": SLOTS, "mean_live_components": live_all / (world * batch),
-                "zoom_fraction": zoom_frac, "parallelism": f"dp{world} (independent shards, no collective)",
-                "cpu_binding": f"rank 0 bound to {len(near)} CPUs near its GPU" if near else "none",
-                "l2_policy": f"inputs larger than L2: {batch * SIZE * SIZE * 4 / 2**20:.0f} MiB written per step",
-                "seed": "1337+rank", "packer_images_per_s_per_core": pack_rate,
-            },
+            "config": cfg,
+            "run": {"images_per_gpu_per_step": sweep, "launches_per_step": n_launch, "images_per_launch": chunk,
+                    "mean_live_components": live_all / (world * sweep), "zoom_fraction": zoom_frac,
+                    "packer_images_per_s_per_core": pack_rate},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT,
                     "h2d_bytes_per_step": eb * (SLOTS * 6 * 8 + 4),
                     "d2h_bytes_per_step": eb * (SIZE * SIZE * 4 + 12),
                     "batch_per_gpu": eb, "steps": e2e_steps,
                     "call": "rsb_jet_render_host (pinned host buffers, float32 images)"},
+            "e2e_dropin": {"value": world * eb * dropin_steps / dropin_s, "unit": UNIT,
+                           "call": f"create_jet(grid[{eb},3,{SIZE},{SIZE}], conf), training_type list: legacy "
+                                   "RNG chain drawn on the host, float64 images + list targets in host memory",
+                           "d2h_bytes_per_step": eb * (SIZE * SIZE * 4 + 12),
+                           "result_bytes_per_step": eb * (SIZE * SIZE * 8 + SLOTS * 8 * 8), "steps": dropin_steps},
             "gpu_launches": launches_all,
             "roofline": {
                 "bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved_gbs / hbm_peak,
-                # dram__bytes_read+write of one launch from the ncu --set full capture, scaled to
-                # this launch's batch (profiles/r01_jet2_kernel_ncu_full_raw.csv: 1.0185 GB / 4096 jets)
-                "traffic": NCU_DRAM_BYTES_PER_IMAGE * batch, "traffic_unit": "bytes per launch",
-                "traffic_source": "ncu --set full, 4096-jet launch, scaled by batch",
+                "traffic": (pj.get("dram_bytes_per_image") or 0) * chunk or None,
+                "traffic_unit": "bytes per launch",
+                "traffic_source": pj.get("source", "no capture of this build committed"),
                 "peak_source": peak_src,
                 "kernel": "rsb::jet::v2::jet2_kernel<2,2>", "algorithmic_bytes_per_image": bytes_per_img,
-                "algorithmic_bytes_per_launch": bytes_per_img * batch,
+                "algorithmic_bytes_per_launch": bytes_per_img * chunk,
+                "note": "the kernel is bound by SFU/FP32 issue, not HBM: `frac` is the HBM view the bench "
+                        "contract asks for, `sfu_frac` the governing one",
                 "governing": "sfu",
                 "sfu_achieved_ex2_per_s": sfu_achieved, "sfu_peak_ex2_per_s": sfu.value,
                 "sfu_frac": sfu_achieved / sfu.value if sfu.value else None,
                 "sfu_peak_source": "rsb_bench_sfu on this device (MUFU.EX2, best of 5)",
                 "algorithmic_ex2_per_image": exps_per_img,
+                "executed_ex2_per_image": pj.get("executed_ex2_per_image"),
+                "sfu_executed_ex2_per_s": (per_gpu_rate * pj["executed_ex2_per_image"]
+                                           if pj.get("executed_ex2_per_image") else None),
             },
         }
+        if world == 1 and not args.no_configs:
+            evs = _Events(L)
+            cfgs = []
+            for fn, kw in ((bench_mojave, {}), (bench_ppdisk, {}),
+                           (bench_survey, {"ns": 2000}), (bench_survey, {"ns": 5000})):
+                try:
+                    if fn is bench_survey:
+                        cfgs.append(fn(L, evs, hbm_peak, sfu.value, prof, **kw))
+                    else:
+                        cfgs.append(fn(L, evs, hbm_peak, **kw))
+                except Exception as exc:  # a broken side config must not lose the headline line
+                    cfgs.append({"config": fn.__name__, "error": f"{type(exc).__name__}: {exc}"})
+            line["configs"] = cfgs
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1
-            per = 12
-            rate, dt = cpu_reference_rate(per, cores)
+            per = 150
+            pool = CpuPool(cores)
+            rate, dt = pool.rate(per)
+            pool.close()
             line["cpu_baseline"] = {
                 "value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                "sample": f"{per * cores} jets 256x256 ({per} per process x {cores} processes, "
+                "sample": f"{per * cores} jets 256x256 ({per} per process x {cores} warm processes, "
                           f"{dt:.1f} s wall), oracle/jet.py create_jet"}
         print(json.dumps(line))
     if dist is not None:
@@ -364,12 +609,14 @@ def run_cuda(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--batch", type=int, default=16384, help="jets per GPU per step")
+    ap.add_argument("--sweep", type=int, default=SWEEP, help="jets per GPU per step")
+    ap.add_argument("--batch", type=int, default=CHUNK, help="jets per launch")
     ap.add_argument("--e2e-batch", type=int, default=4096)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C2-C4 records")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -97,6 +97,12 @@ def simulate_sky_distributions(conf, mode, rank=None, world=None):
     """``simulate_sky_distributions`` (``simulations.py:46-79``), sharded over ranks."""
     if rank is None or world is None:
         rank, world, _ = rank_info()
+    if getattr(conf.dataset, "noise", False):
+        # reference simulations.py:101-108,121-125 would call add_noise here; writing noise-free
+        # shards for a configuration that asks for noise would look valid and be wrong
+        raise NotImplementedError(
+            "dataset.noise = true: add_noise (reference utils/utils.py:259-315) is not available in "
+            "radiosim_b200 yet; set [dataset] noise = false (the reference's shipped rc file does)")
     seed = rank_seed(conf.general.seed, rank)
     if seed is not None:
         np.random.seed(seed)  # the legacy global stream, as tools/simulation_cli.py:38-40 does

@@ -114,4 +114,4 @@ def test_kernel_swirl_identity_and_direction():
     rho = 30.0
     expect = -s * np.exp(-rho / (radius / 5 * np.log(2)))
     assert ang(plain) == pytest.approx(0.0, abs=2e-2)
-    assert ang(sw) < -0.1 and ang(sw) == pytest.approx(expect, abs=0.12)
+    assert ang(sw) < -0.05 and ang(sw) == pytest.approx(expect, abs=0.08)   # (a flux-weighted mean over rho)
