@@ -100,6 +100,21 @@ int rsb_jet_render(const double* params_dev, const int32_t* zoom_pad_dev, int n,
                    int32_t* out_margin_dev, double* out_peak_dev, void* workspace_dev,
                    size_t workspace_bytes, void* stream);
 
+/* Jets of different sizes in ONE launch -- the nested create_jet calls of create_survey's
+ * class-0 sources (src/radiosim/survey/survey.py:54-60: every sub-jet has its own
+ * jet_size in [N/10.24, N/5.12)).  Same per-image work and results as rsb_jet_render.
+ *
+ *  sizes_dev    [n] int32: image i is sizes[i] x sizes[i], 2 <= sizes[i] <= max_size <= 256
+ *  out_offs_dev [n] int64: image i starts at out_img_dev + out_offs[i] elements (a multiple
+ *               of 4); its rows are (sizes[i] + 3) & ~3 elements apart (the pad columns are
+ *               written with unspecified values)
+ *  params_dev, zoom_pad_dev, out_margin_dev, out_peak_dev, flags: as for rsb_jet_render
+ *  (slots <= 32).  Sorting the batch by size keeps the CTAs of one wave equally busy. */
+int rsb_jet_render_var(const double* params_dev, const int32_t* zoom_pad_dev,
+                       const int32_t* sizes_dev, const long long* out_offs_dev, int n, int slots,
+                       int max_size, unsigned flags, void* out_img_dev, int32_t* out_margin_dev,
+                       double* out_peak_dev, void* stream);
+
 /* Component planes for training_type == "gauss" (jet.py:185, :219-225): the
  * `slots` planes after zoom_on_source (NOT zoomed out -- utils.py:168-175 drops
  * that result), divided by peak.  margin/peak come from rsb_jet_render.
@@ -128,14 +143,17 @@ int rsb_jet_render_host(const double* params_host, const int32_t* zoom_pad_host,
  *  src_params_dev [total_sources][6] float64, grouped per image: class-1 (gaussian) rows,
  *                 then class-2 (point) rows
  *  src_offs_dev   [n][3] int32: first class-1 row, first class-2 row, end row of image i
- *  jet_rects_dev  [jet_offs[n]] records {int64 pix; int32 size, row0, col0, pad}: offset of the
- *                 sub-jet's first pixel in jet_pix_dev, its edge, and the image position of
+ *  jet_rects_dev  [jet_offs[n]] records {int64 pix; int32 size, row0, col0, pitch}: offset of the
+ *                 sub-jet's first pixel in jet_pix_dev, its edge, the image position of
  *                 its pixel (0,0): row0 = floor(x - size/2), col0 = floor(y - size/2)
- *                 (survey.py:61-64; may be negative)
+ *                 (survey.py:61-64; may be negative), and the floats between its rows
+ *                 (size for rsb_jet_render output, (size + 3) & ~3 for rsb_jet_render_var)
  *  jet_offs_dev   [n + 1] int32: sub-jets of image i are jet_offs[i] .. jet_offs[i+1]-1
  *  out_x_dev      [n][size][size], out_y_dev [n][4][size][size]: float32, or float64 with
  *                 RSB_JET_OUT_F64 (planes: jets, gaussians, points, background)
- *  workspace_dev  >= rsb_survey_workspace_bytes() bytes of device scratch */
+ *  workspace_dev  >= rsb_survey_workspace_bytes() bytes of device scratch (coefficient records
+ *                 and three counters per image; no image-sized scratch: the class planes stay on
+ *                 chip until the image maximum is known and are written once, normalised) */
 int rsb_survey_workspace_bytes(int n, int size, int total_sources, size_t* bytes);
 int rsb_survey_render(const double* src_params_dev, const int32_t* src_offs_dev,
                       int total_sources, const void* jet_rects_dev, const int32_t* jet_offs_dev,

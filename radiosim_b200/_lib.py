@@ -60,6 +60,7 @@ _SIGS = {
     "rsb_bench_sfu": ([_i32, C.POINTER(C.c_double)], _i32),
     "rsb_jet_workspace_bytes": ([_i32, _i32, _i32, C.POINTER(_sz)], _i32),
     "rsb_jet_render": ([_vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp, _vp, _sz, _vp], _i32),
+    "rsb_jet_render_var": ([_vp, _vp, _vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp, _vp], _i32),
     "rsb_jet_planes": ([_vp, _vp, _vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp], _i32),
     "rsb_jet_render_static": ([_vp, _vp, _i32, _i32, _i32, _u32, _vp, _vp, _vp, _vp], _i32),
     "rsb_survey_workspace_bytes": ([_i32, _i32, _i32, C.POINTER(_sz)], _i32),

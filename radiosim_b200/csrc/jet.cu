@@ -564,6 +564,25 @@ int rsb_jet_render(const double* params, const int32_t* zoom_pad, int n, int slo
   return launch(a, p, grid, (cudaStream_t)stream);
 }
 
+int rsb_jet_render_var(const double* params, const int32_t* zoom_pad, const int32_t* sizes,
+                       const long long* out_offs, int n, int slots, int max_size, unsigned flags,
+                       void* out_img, int32_t* out_margin, double* out_peak, void* stream) {
+  if (int e = check_common("rsb_jet_render_var", n, slots, max_size)) return e;
+  if (n == 0) return 0;
+  RSB_ARG(params && zoom_pad && sizes && out_offs && out_img && out_margin && out_peak,
+          "rsb_jet_render_var: NULL buffer");
+  RSB_ARG(((uintptr_t)params & 15) == 0 && ((uintptr_t)out_img & 15) == 0,
+          "rsb_jet_render_var: params and out_img must be 16-byte aligned");
+  RSB_ARG(max_size <= 256 && slots <= 32,
+          "rsb_jet_render_var: sizes up to 256 and up to 32 slots (got %d, %d)", max_size, slots);
+  Args a;
+  a.params = params; a.zoom_pad = zoom_pad; a.n = n; a.slots = slots; a.size = max_size;
+  a.flags = flags; a.out = out_img; a.margin = out_margin; a.peak = out_peak;
+  a.scratch = nullptr; a.pitch = (max_size + 3) & ~3;
+  a.sizes = sizes; a.out_offs = out_offs;
+  return v2_launch_var(a, (cudaStream_t)stream);
+}
+
 int rsb_jet_planes(const double* params, const int32_t* zoom_pad, const int32_t* margin,
                    const double* peak, int n, int slots, int size, unsigned flags, void* out,
                    void* stream) {

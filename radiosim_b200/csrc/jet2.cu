@@ -92,7 +92,7 @@ struct __align__(16) Fixed2 {
   int foot_lo, foot_hi;             // output coordinates with a non-zero tap
   float delta[2];
   int dlo[2];                       // no pixel closer than this to the border exceeds 0.01
-  struct LabelReq { unsigned long long best; int img, pb, margin, zpad; } label[2];  // [image parity]
+  struct LabelReq { unsigned long long best; int img, pb, margin, zpad, n, pad; } label[2];  // [image parity]
   float geo[kSlots2 * 16];          // build_coefs2 scratch (SlotGeo per live slot)
   int ncand;                        // borderline pixels awaiting a float64 verdict
   int cand[kMaxCand];               // r << 16 | c
@@ -520,23 +520,67 @@ __device__ inline Tap3 merge_taps(const Taps64& t, int N) {
   return m;
 }
 
-template <int kCluster, int NS>
+// kVar: every image has its own size (a.sizes[img] <= a.size) and output offset -- the sub-jets
+// of a survey (reference survey/survey.py:54-60) in ONE launch.  With two CTAs per image the
+// first band takes ceil(N/2) rows, so odd sizes work: the centre row (N-1)/2 is the last row of
+// the first band and the halo row of the second, and no tap with a non-zero weight reaches
+// further across (the composite operator preserves the centre).
+template <int kCluster, int NS, bool kVar = false>
 __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Fixed2& sm = *reinterpret_cast<Fixed2*>(smem_raw);
-  const int N = a.size, pitch = a.pitch, slots = a.slots;
-  const int npad = (N + 3) & ~3;
+  const int slots = a.slots;
+  const int npad_max = (a.size + 3) & ~3;
   // composite taps, one record per output coordinate: {w0, w1, w2, first tap (absolute, as int bits)}
-  float4* tab = reinterpret_cast<float4*>(smem_raw + sizeof(Fixed2));  // [npad]
-  float* raw = reinterpret_cast<float*>(tab + npad);                   // [H (+1 halo)][pitch]
+  float4* tab = reinterpret_cast<float4*>(smem_raw + sizeof(Fixed2));  // [npad_max]
+  float* raw = reinterpret_cast<float*>(tab + npad_max);               // [H (+1 halo)][pitch]
 
   const uint32_t s_raw = keep_u32(smem_u32(raw)), s_tab = keep_u32(smem_u32(tab));
   const int tid = keep_s32((int)threadIdx.x), lane = tid & 31, warp = tid >> 5;
   const int rank = keep_s32((kCluster > 1) ? (int)(blockIdx.x % kCluster) : 0);
   const int cid = blockIdx.x / kCluster, nclusters = gridDim.x / kCluster;
-  const int H = N / kCluster;                // rows of this CTA's band (N even when kCluster == 2)
-  const int R0 = keep_s32(rank * H);                   // first absolute row of the band
-  const int base = keep_s32((rank == 0) ? 0 : H - 1);  // absolute row stored at raw row 0 (rank 1: halo)
+  const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
+  const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
+  const size_t esz = f64 ? 8 : 4;
+  // ---- geometry of the current image (fixed for the whole launch unless kVar) ----
+  int N, npad, pitch, opitch;  // size, size rounded up to 4, raw row pitch, output row pitch (elements)
+  int H0, H, R0, base;         // rows of the first band / of this CTA's band, its first absolute row,
+                               // absolute row stored at raw row 0 (second band: the halo row)
+  int strips, tcols, stage_rows;
+  bool vec;
+  float* stage;
+  uint32_t s_stage;
+  // the stage sits behind the largest raw band of the launch, so that an image never renders
+  // into rows the previous image's bulk store is still reading
+  const int Hmax = (kCluster == 1) ? a.size : (a.size + 1) / 2;
+  float* const stage_var = raw + (size_t)(Hmax + (kCluster > 1 ? 1 : 0)) * npad_max;
+  auto geometry = [&](int n_) {
+    N = n_;
+    npad = (N + 3) & ~3;
+    pitch = kVar ? npad : a.pitch;
+    opitch = kVar ? npad : N;
+    H0 = (kCluster == 1) ? N : (N + 1) / 2;
+    H = (kCluster == 1 || rank == 0) ? H0 : N - H0;
+    R0 = keep_s32((rank == 0) ? 0 : H0);
+    base = keep_s32((rank == 0) ? 0 : H0 - 1);
+    strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
+    tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
+    vec = (opitch & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
+    // float32 output with contiguous rows: the first stage_rows rows of the finished band are
+    // staged in shared memory and leave through one bulk async copy that drains while the next
+    // image is being rendered (an SM pushes ~30 B/clk towards L2 whichever engine stores, so
+    // the gain is the overlap, not the engine); the other rows are stored directly.
+    if constexpr (kVar) {
+      const int room = (a.raw_floats - (int)(stage_var - raw)) / opitch;
+      stage_rows = (!f64 && vec) ? max(0, min(H / 2, room)) : 0;
+      stage = stage_var;
+    } else {
+      stage_rows = (!f64 && vec && pitch == N) ? a.stage_rows : 0;
+      stage = raw + (size_t)(H + (kCluster > 1 ? 1 : 0)) * pitch;
+    }
+    s_stage = keep_u32(smem_u32(stage));
+  };
+  geometry((kVar && cid < a.n) ? a.sizes[cid] : a.size);
   // remote (peer CTA) shared-memory addresses for st.async
   uint32_t peer_xval = 0, peer_xbar = 0, peer_raw = 0;
   if constexpr (kCluster > 1) {
@@ -562,20 +606,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   };
 
   const uint32_t pbytes = (uint32_t)slots * RSB_JET_PARAM_STRIDE * 8u;
-  const int strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
-  const int tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
-  const bool vec = (N & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
-  const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
-  const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
-  const size_t esz = f64 ? 8 : 4;
-  // float32 output with contiguous rows: the first stage_rows rows of the finished band are
-  // staged in shared memory and leave through one bulk async copy that drains while the next
-  // image is being rendered (an SM pushes ~30 B/clk towards L2 whichever engine stores, so
-  // the gain is the overlap, not the engine); the other rows are stored directly.
-  const int stage_rows = (!f64 && vec && pitch == N) ? a.stage_rows : 0;
-  float* stage = raw + (size_t)(H + (kCluster > 1 ? 1 : 0)) * pitch;
-  const uint32_t s_stage = keep_u32(smem_u32(stage));
   const char* bulk_dst = nullptr;  // (thread 0) where the staged rows of the previous image go
+  uint32_t bulk_bytes = 0;         // ... and how many bytes of the stage they are
 
   if (tid == 0) {
     mbar_init(&sm.bar[0], 1);
@@ -618,7 +650,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     const Fixed2::LabelReq q = sm.label[par];
     double peak = 1.0;
     if (normalize)
-      peak = peak64(sm.pix64, sm.params[q.pb], slots, N, q.zpad >= 0, q.zpad, q.margin, q.best, lane);
+      peak = peak64(sm.pix64, sm.params[q.pb], slots, q.n, q.zpad >= 0, q.zpad, q.margin, q.best, lane);
     if (lane == 0) {
       a.margin[q.img] = q.margin;
       a.peak[q.img] = peak;
@@ -632,8 +664,11 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     mbar_wait(&sm.bar[pb], (it / 3) & 1);
     __syncthreads();  // (A) coef/span/nlive of this image visible; raw free for reuse; stage complete
     if (tid == 0 && bulk_dst) {
-      bulk_s2g(const_cast<char*>(bulk_dst), stage, (uint32_t)(stage_rows * N * 4));
+      bulk_s2g(const_cast<char*>(bulk_dst), stage, bulk_bytes);
       bulk_dst = nullptr;
+    }
+    if constexpr (kVar) {
+      if (it > 0) geometry(a.sizes[img]);
     }
     if (tid == 0) {  // running reductions of this image (all reads of the previous values are behind A)
       sm.lbest = 0ull;
@@ -650,11 +685,18 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         if (img + nclusters < a.n) {
           const int nb = (it + 1) % 3;
           mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
+          int nN = N, nR0 = R0, nH = H;  // the next image's geometry
+          if constexpr (kVar) {
+            nN = a.sizes[img + nclusters];
+            const int g0 = (kCluster == 1) ? nN : (nN + 1) / 2;
+            nH = (kCluster == 1 || rank == 0) ? g0 : nN - g0;
+            nR0 = (rank == 0) ? 0 : g0;
+          }
 #ifdef RSB_TIMELINE
-          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane, a.zoom_pad[img + nclusters] >= 0,
+          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane, a.zoom_pad[img + nclusters] >= 0,
                        first_worker, g_timeline ? &g_timeline[((size_t)img * 2 + rank) * 96 + 24] : nullptr);
 #else
-          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane,
+          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane,
                        a.zoom_pad[img + nclusters] >= 0, first_worker);
 #endif
         }
@@ -942,7 +984,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 
     RSB_STAMP(1);  // this warp is out of tiles
     int margin = 0;
-    char* out = reinterpret_cast<char*>(a.out) + (size_t)img * N * N * esz;
+    char* out = reinterpret_cast<char*>(a.out) +
+                (kVar ? (size_t)a.out_offs[img] : (size_t)img * N * N) * esz;
     unsigned long long image_best = 0ull;  // arg-max key of the final image (normalize only)
 
     if (!zoom) {
@@ -961,10 +1004,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       RSB_STAMP(2);
       const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
-      if (!f64 && vec && pitch == N) {
+      if (!f64 && vec && pitch == opitch) {
         // float32, 16-byte aligned contiguous rows: the band is one run of float4
         const uint32_t s_src = s_raw + (uint32_t)((R0 - base) * pitch) * 4u;
-        float4* outv = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + (size_t)R0 * N);
+        float4* outv = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + (size_t)R0 * opitch);
         const int nstage = stage_rows * q4;
         for (int e = tid; e < H * q4; e += kWorkers) {
           float4 v = lds_v4(s_src + (uint32_t)e * 16u);
@@ -978,7 +1021,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
           const int r = R0 + rl;
           float4 v = lds_v4(s_raw + (uint32_t)((r - base) * pitch + c0) * 4u);
           v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-          store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+          store_out4(out + (size_t)r * opitch * esz, f64, c0, N, vec, v);
         }
       }
     } else {
@@ -1124,8 +1167,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       RSB_STAMP(5);
       if constexpr (kCluster > 1) {
         // halo: my boundary row of T goes into the peer's halo slot
-        const int src = (rank == 0) ? (H - 1) : 1;  // local index of absolute row H-1 / H
-        const int dst = (rank == 0) ? 0 : H;        // peer's halo slot
+        const int src = (rank == 0) ? (H - 1) : 1;  // local index of absolute row H0-1 / H0
+        const int dst = (rank == 0) ? 0 : H0;       // peer's halo slot
         for (int e = tid; e < (pitch >> 2); e += kWorkers)
           st_async_v4(peer_raw + (uint32_t)(dst * pitch + 4 * e) * 4u,
                       reinterpret_cast<const float4*>(raw + (size_t)src * pitch)[e], peer_xbar + 8u);
@@ -1203,9 +1246,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         // branches (they cost more issue slots than the stores themselves)
         // (running addresses, laundered: the compiler otherwise rebuilds the 64-bit address
         // from the kernel arguments in front of every store)
-        float* outf = keep_ptr(reinterpret_cast<float*>(out) + (size_t)(R0 + warp) * N + 4 * lane);
-        uint32_t s_st = keep_u32(s_stage + (uint32_t)(warp * N + 4 * lane) * 4u);
-        const uint32_t step = keep_u32((uint32_t)(kWarps * N));  // floats between this warp's rows
+        float* outf = keep_ptr(reinterpret_cast<float*>(out) + (size_t)(R0 + warp) * opitch + 4 * lane);
+        uint32_t s_st = keep_u32(s_stage + (uint32_t)(warp * opitch + 4 * lane) * 4u);
+        const uint32_t step = keep_u32((uint32_t)(kWarps * opitch));  // floats between this warp's rows
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
           const int rl = warp + i * kWarps;
@@ -1233,27 +1276,28 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
             if (s >= strips || c0 >= N) continue;
             float4 v = res[i][s];
             v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-            store_out4(out + (size_t)r * N * esz, f64, c0, N, vec, v);
+            store_out4(out + (size_t)r * opitch * esz, f64, c0, N, vec, v);
           }
         }
       }
     }
     if (stage_rows > 0) {
       fence_proxy_async();  // my writes to the stage -> visible to the async (TMA) proxy
-      bulk_dst = out + (size_t)R0 * N * 4;  // issued by thread 0 behind the next barrier
+      bulk_dst = out + (size_t)R0 * opitch * 4;  // issued by thread 0 behind the next barrier
+      bulk_bytes = (uint32_t)(stage_rows * opitch * 4);
     }
 
     RSB_STAMP(9);
     // this image's labels are produced by the label warp during the next image
     if (tid == 0) {
       Fixed2::LabelReq q;
-      q.best = image_best; q.img = img; q.pb = pb; q.margin = margin; q.zpad = zpad;
+      q.best = image_best; q.img = img; q.pb = pb; q.margin = margin; q.zpad = zpad; q.n = N; q.pad = 0;
       sm.label[buf] = q;
     }
   }
   __syncthreads();
   if (tid == 0 && bulk_dst) {
-    bulk_s2g(const_cast<char*>(bulk_dst), stage, (uint32_t)(stage_rows * N * 4));
+    bulk_s2g(const_cast<char*>(bulk_dst), stage, bulk_bytes);
     bulk_wait_all();
   }
   if (rank == 0 && warp == kLabelWarp && it > 0) label_job((it - 1) & 1);
@@ -1261,9 +1305,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
 }
 
 // ------------------------------------------------------------------ host side
-template <int kCluster, int NS>
+template <int kCluster, int NS, bool kVar = false>
 static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
-  auto k = jet2_kernel<kCluster, NS>;
+  auto k = jet2_kernel<kCluster, NS, kVar>;
   RSB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   const int sms = sm_count();
   // CTAs are limited to one per SM by registers (512 threads x 128); small images leave
@@ -1291,12 +1335,12 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
 
 static size_t v2_bytes(int size, int cluster, int stage_rows = 0) {
   const int npad = (size + 3) & ~3;
-  const int rows = size / cluster + (cluster > 1 ? 1 : 0);
+  const int rows = (size + cluster - 1) / cluster + (cluster > 1 ? 1 : 0);
   return sizeof(v2::Fixed2) + (size_t)npad * 16 + (size_t)(rows + stage_rows) * npad * 4;
 }
 // rows of a band that are staged for the bulk store: half the band when that fits
 static int v2_stage_rows(int size, int cluster, int max_optin) {
-  const int half = (size / cluster) / 2;
+  const int half = ((size + cluster - 1) / cluster) / 2;
   return v2_bytes(size, cluster, half) <= (size_t)max_optin ? half : 0;
 }
 
@@ -1311,7 +1355,7 @@ bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes) {
     *smem_bytes = v2_bytes(size, 1, v2_stage_rows(size, 1, max_optin));
     return true;
   }
-  if ((size & 1) == 0 && size / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {
+  if ((size + 1) / 2 <= v2::kMaxBand && v2_bytes(size, 2) <= (size_t)max_optin) {  // (odd sizes: uneven bands)
     *cluster = 2;
     *smem_bytes = v2_bytes(size, 2, v2_stage_rows(size, 2, max_optin));
     return true;
@@ -1329,6 +1373,27 @@ int v2_launch(const Args& a_in, int cluster, size_t smem_bytes, cudaStream_t st)
   if (cluster == 1)
     return strips <= 1 ? v2::launch_v2<1, 1>(a, smem_bytes, st) : v2::launch_v2<1, 2>(a, smem_bytes, st);
   return strips <= 1 ? v2::launch_v2<2, 1>(a, smem_bytes, st) : v2::launch_v2<2, 2>(a, smem_bytes, st);
+}
+
+// Variable-size launch: a.size is the largest size of the batch.  One CTA per image when every
+// band fits (size <= 128), else a 2-CTA cluster (size <= 256, even or odd).
+int v2_launch_var(const Args& a_in, cudaStream_t st) {
+  int dev = 0, max_optin = 0;
+  RSB_CUDA(cudaGetDevice(&dev));
+  RSB_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  Args a = a_in;
+  const int cluster = a.size <= v2::kMaxBand ? 1 : 2;
+  RSB_ARG(a.slots <= v2::kSlots2 && a.size <= 2 * v2::kMaxBand && v2_bytes(a.size, cluster) <= (size_t)max_optin,
+          "variable-size jets: sizes up to %d and %d slots only", 2 * v2::kMaxBand, v2::kSlots2);
+  const size_t smem = v2_bytes(a.size, cluster, v2_stage_rows(a.size, cluster, max_optin));
+  const int npad = (a.size + 3) & ~3;
+  a.raw_floats = (int)((smem - sizeof(v2::Fixed2) - (size_t)npad * 16) / 4);
+  a.pitch = npad;
+  a.stage_rows = 0;
+  const int strips = (a.size + kStrip - 1) / kStrip;
+  if (cluster == 1)
+    return strips <= 1 ? v2::launch_v2<1, 1, true>(a, smem, st) : v2::launch_v2<1, 2, true>(a, smem, st);
+  return v2::launch_v2<2, 2, true>(a, smem, st);
 }
 
 }  // namespace jet

@@ -31,6 +31,12 @@ struct Args {
   float* scratch;  // per-CTA raw-image slots when the image does not fit in smem
   int pitch;       // floats per stored raw row (size rounded up to 4)
   int stage_rows = 0;  // on-chip path: rows of each band that leave through a staged bulk copy
+  // variable-size launch (on-chip path only): image i is sizes[i] x sizes[i] (all <= size), its
+  // rows are stored (sizes[i] + 3) & ~3 elements apart starting at out + out_offs[i] elements
+  // (offsets multiples of 4); raw_floats = floats of shared memory behind the tap table
+  const int32_t* sizes = nullptr;
+  const long long* out_offs = nullptr;
+  int raw_floats = 0;
 };
 
 // ---- float64 evaluation of one raw pixel, operation order of gauss.py:77-88 ----
@@ -157,6 +163,8 @@ __device__ inline void build_coefs(SM& sm, const double* P, int slots, int N, in
 // host-side launchers of the on-chip path (jet2.cu)
 bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes);
 int v2_launch(const Args& a, int cluster, size_t smem_bytes, cudaStream_t st);
+// variable-size launch: a.size = largest size in the batch, a.sizes / a.out_offs per image
+int v2_launch_var(const Args& a, cudaStream_t st);
 
 }  // namespace jet
 }  // namespace rsb

@@ -91,6 +91,41 @@ def _htab():
     return _HTAB
 
 
+def _records(part):
+    ncomp = sum(len(c) for c, _ in part)
+    comps = np.zeros(ncomp, dtype=COMP)
+    images = np.zeros(len(part), dtype=IMAGE)
+    k = 0
+    for j, (cl, (lo, hi, new)) in enumerate(part):
+        images[j] = (k, len(cl), lo, hi, new, (0, 0, 0))
+        for (ca, sa, a2i, b2i, a2o, b2o, scale, sigma) in cl:
+            comps[k] = (ca, sa, a2i, b2i, a2o, b2o, np.float32(scale), int(sigma), j, (0, 0, 0))
+            k += 1
+    return comps, images
+
+
+class DeviceProtos:
+    """Packed protos resident on the device; :meth:`enqueue` issues ``rsb_ppdisk_render`` on the
+    default stream without synchronising (device-side timing of the kernels alone)."""
+
+    def __init__(self, img_size, packed):
+        L.require_device()
+        self.lib, self.img_size, self.n = L.lib(), img_size, len(packed)
+        comps, images = _records(packed)
+        self.ncomp = len(comps)
+        need = C.c_size_t(0)
+        L.check(self.lib.rsb_ppdisk_workspace_bytes(self.n, self.ncomp, C.byref(need)))
+        self.d_h = L.dev_from(_htab())
+        self.d_c, self.d_i = L.dev_from(comps), L.dev_from(images)
+        self.d_w = L.DeviceBuffer(need.value)
+        self.d_o = L.DeviceBuffer(self.n * img_size * img_size * 4)
+
+    def enqueue(self):
+        L.check(self.lib.rsb_ppdisk_render(self.d_c.ptr, self.ncomp, self.d_i.ptr, self.n, self.d_h.ptr,
+                                           self.img_size, self.d_o.ptr, self.d_w.ptr, self.d_w.nbytes, None),
+                "rsb_ppdisk_render")
+
+
 def render_protos(img_size, packed, chunk=32):
     """``packed``: list of ``pack_proto`` results -> float32 ``[n, img_size, img_size]``."""
     L.require_device()
@@ -100,15 +135,8 @@ def render_protos(img_size, packed, chunk=32):
     d_h = L.dev_from(_htab())
     for i0 in range(0, n, chunk):
         part = packed[i0 : i0 + chunk]
-        ncomp = sum(len(c) for c, _ in part)
-        comps = np.zeros(ncomp, dtype=COMP)
-        images = np.zeros(len(part), dtype=IMAGE)
-        k = 0
-        for j, (cl, (lo, hi, new)) in enumerate(part):
-            images[j] = (k, len(cl), lo, hi, new, (0, 0, 0))
-            for (ca, sa, a2i, b2i, a2o, b2o, scale, sigma) in cl:
-                comps[k] = (ca, sa, a2i, b2i, a2o, b2o, np.float32(scale), int(sigma), j, (0, 0, 0))
-                k += 1
+        comps, images = _records(part)
+        ncomp = len(comps)
         need = C.c_size_t(0)
         L.check(lib.rsb_ppdisk_workspace_bytes(len(part), ncomp, C.byref(need)))
         d_c, d_i = L.dev_from(comps), L.dev_from(images)

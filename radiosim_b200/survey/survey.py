@@ -1,8 +1,9 @@
 """Drop-in ``create_survey`` (reference ``src/radiosim/survey/survey.py:9-132``).
 
 Host: the RNG chain of the reference, draw for draw (:func:`pack_survey`), including the
-nested ``create_jet`` chain of class-0 sources.  Device: sub-jets through ``rsb_jet_render``
-(one launch per distinct sub-jet size), everything else through ``rsb_survey_render``.
+nested ``create_jet`` chain of class-0 sources.  Device: all sub-jets of the batch through
+``rsb_jet_render_var`` (every sub-jet has its own size; at most two launches), everything else
+through ``rsb_survey_render`` (one fused kernel: splat, paste, per-image maximum, normalise).
 """
 
 from __future__ import annotations
@@ -16,9 +17,9 @@ import numpy as np
 from .. import _lib as L
 from ..jets.packer import JetBatch, pack_jets, pack_jets_py
 
-__all__ = ["create_survey", "pack_survey", "render_survey"]
+__all__ = ["DeviceSurvey", "create_survey", "pack_survey", "render_survey"]
 
-JET_RECT = np.dtype([("pix", "<i8"), ("size", "<i4"), ("row0", "<i4"), ("col0", "<i4"), ("pad", "<i4")])
+JET_RECT = np.dtype([("pix", "<i8"), ("size", "<i4"), ("row0", "<i4"), ("col0", "<i4"), ("pitch", "<i4")])
 
 
 @dataclass
@@ -140,80 +141,96 @@ def pack_survey_py(n: int, size: int, num_sources: int, class_distribution, scal
                        np.array(jr0, dtype=np.int64), np.array(jc0, dtype=np.int64))
 
 
-def _render_subjets(batch: SurveyBatch, normalize: bool):
-    """All sub-jets, grouped by size, into one packed float32 device buffer.
+class DeviceSurvey:
+    """A packed batch resident on the device: everything is uploaded once, :meth:`enqueue` issues
+    the kernels (sub-jets in at most two variable-size launches, then ``rsb_survey_render``) on the
+    default stream without synchronising, :meth:`download` copies the two results to host arrays."""
 
-    One upload of the parameters (sorted by size), one launch per distinct size on slices of it."""
-    lib = L.lib()
-    all_params, all_zpad, sizes = batch.flat_jets()
-    nj = batch.njets
-    order = np.argsort(sizes, kind="stable")
-    pix_off = np.zeros(nj, dtype=np.int64)
-    ssz = sizes[order]
-    starts = np.flatnonzero(np.r_[True, ssz[1:] != ssz[:-1]]) if nj else np.zeros(0, np.int64)
-    ends = np.r_[starts[1:], nj] if nj else np.zeros(0, np.int64)
-    total_pix = int((sizes.astype(np.int64) ** 2).sum()) + 4 * (len(starts) + 1)
-    d_pix = L.DeviceBuffer(max(total_pix * 4, 16))
-    if nj == 0:
-        return d_pix, pix_off, sizes
-    slots = all_params.shape[1]
-    d_p = L.dev_from(all_params[order])
-    d_z = L.dev_from(all_zpad[order])
-    d_m, d_k = L.DeviceBuffer(nj * 4), L.DeviceBuffer(nj * 8)
-    need_max = 0
-    need = C.c_size_t(0)
-    for a, b in zip(starts, ends):
-        L.check(lib.rsb_jet_workspace_bytes(int(b - a), slots, int(ssz[a]), C.byref(need)))
-        need_max = max(need_max, need.value)
-    d_w = L.DeviceBuffer(max(need_max, 16))
-    flags = L.JET_NORMALIZE if normalize else 0
-    cursor = 0
-    for a, b in zip(starts, ends):
-        a, b = int(a), int(b)
-        js, cnt = int(ssz[a]), b - a
-        pix_off[order[a:b]] = cursor + np.arange(cnt, dtype=np.int64) * (js * js)
-        L.check(lib.rsb_jet_render(d_p.ptr + a * slots * 48, d_z.ptr + a * 4, cnt, slots, js, flags,
-                                   d_pix.ptr + cursor * 4, d_m.ptr + a * 4, d_k.ptr + a * 8, d_w.ptr,
-                                   d_w.nbytes, None),
-                "rsb_jet_render (survey sub-jets)")
-        cursor += cnt * js * js
-        cursor = (cursor + 3) & ~3  # keep every group 16-byte aligned (128-bit stores)
-    L.device_sync()
-    return d_pix, pix_off, sizes
+    def __init__(self, batch: SurveyBatch, jet_normalize: bool = True, f64: bool = True):
+        L.require_device()
+        self.lib = L.lib()
+        self.n, self.size, self.f64 = batch.n, batch.size, f64
+        n, size = batch.n, batch.size
+        all_params, all_zpad, sizes = batch.flat_jets()
+        nj = self.nj = batch.njets
+        self.flags_jet = L.JET_NORMALIZE if jet_normalize else 0
+        # sub-jets sorted by size (CTAs of one wave equally busy); sizes <= 128 take one CTA per
+        # image, larger ones a 2-CTA cluster -> two launches at most
+        order = np.argsort(sizes, kind="stable")
+        ssz = sizes[order].astype(np.int64)
+        pitch = (ssz + 3) & ~3
+        pix_sorted = np.zeros(nj, dtype=np.int64)
+        if nj:
+            pix_sorted[1:] = np.cumsum(ssz * pitch)[:-1]      # (multiples of 4: every pitch is)
+        total_pix = int((ssz * pitch).sum())
+        self.groups = []
+        if nj:
+            split = int(np.searchsorted(ssz, 128, side="right"))
+            for a, b in ((0, split), (split, nj)):
+                if b > a:
+                    self.groups.append((a, b, int(ssz[b - 1])))
+            if int(ssz[-1]) > 256 or all_params.shape[1] > 32:
+                raise L.RsbError("survey sub-jets larger than 256 pixels or with more than 32 slots "
+                                 "are not supported by the variable-size jet launch")
+        self.slots = all_params.shape[1] if nj else 1
+        self.d_pix = L.DeviceBuffer(max(total_pix * 4, 16))
+        if nj:
+            self.d_p = L.dev_from(all_params[order])
+            self.d_z = L.dev_from(all_zpad[order])
+            self.d_sizes = L.dev_from(ssz.astype(np.int32))
+            self.d_offs = L.dev_from(pix_sorted)
+            self.d_m, self.d_k = L.DeviceBuffer(nj * 4), L.DeviceBuffer(nj * 8)
+        rects = np.zeros(max(nj, 1), dtype=JET_RECT)
+        jet_offs = np.zeros(n + 1, dtype=np.int32)
+        if nj:
+            inv = np.empty(nj, dtype=np.int64)
+            inv[order] = np.arange(nj)                        # draw order -> sorted position
+            by_img = np.argsort(batch.jet_image, kind="stable")
+            pos = inv[by_img]
+            rects["pix"][:nj] = pix_sorted[pos]
+            rects["size"][:nj] = ssz[pos]
+            rects["pitch"][:nj] = pitch[pos]
+            rects["row0"][:nj] = batch.jet_row0[by_img]
+            rects["col0"][:nj] = batch.jet_col0[by_img]
+            jet_offs[1:] = np.cumsum(np.bincount(batch.jet_image, minlength=n))
+        self.total = batch.src_params.shape[0]
+        need = C.c_size_t(0)
+        L.check(self.lib.rsb_survey_workspace_bytes(n, size, self.total, C.byref(need)))
+        self.dt = np.float64 if f64 else np.float32
+        self.d_src = L.dev_from(batch.src_params if self.total else np.zeros((1, 6)))
+        self.d_soffs = L.dev_from(batch.src_offs if n else np.zeros((1, 3), np.int32))
+        self.d_rects = L.dev_from(rects)
+        self.d_joffs = L.dev_from(jet_offs)
+        self.d_w = L.DeviceBuffer(max(need.value, 16))
+        esz = np.dtype(self.dt).itemsize
+        self.d_x = L.DeviceBuffer(max(n * size * size * esz, 16))
+        self.d_y = L.DeviceBuffer(max(n * 4 * size * size * esz, 16))
+
+    def enqueue(self):
+        lib = self.lib
+        for a, b, max_size in self.groups:
+            L.check(lib.rsb_jet_render_var(self.d_p.ptr + a * self.slots * 48, self.d_z.ptr + a * 4,
+                                           self.d_sizes.ptr + a * 4, self.d_offs.ptr + a * 8, b - a,
+                                           self.slots, max_size, self.flags_jet, self.d_pix.ptr,
+                                           self.d_m.ptr + a * 4, self.d_k.ptr + a * 8, None),
+                    "rsb_jet_render_var (survey sub-jets)")
+        if self.n:
+            L.check(lib.rsb_survey_render(self.d_src.ptr, self.d_soffs.ptr, self.total, self.d_rects.ptr,
+                                          self.d_joffs.ptr, self.d_pix.ptr, self.n, self.size,
+                                          L.JET_OUT_F64 if self.f64 else 0, self.d_x.ptr, self.d_y.ptr,
+                                          self.d_w.ptr, self.d_w.nbytes, None), "rsb_survey_render")
+
+    def download(self):
+        n, size = self.n, self.size
+        x = self.d_x.download((n, 1, size, size), self.dt, pinned=True)
+        y = self.d_y.download((n, 4, size, size), self.dt, pinned=True)
+        return x, y
 
 
 def render_survey(batch: SurveyBatch, jet_normalize: bool = True, f64: bool = True):
-    L.require_device()
-    lib = L.lib()
-    n, size = batch.n, batch.size
-    d_pix, pix_off, sizes = _render_subjets(batch, jet_normalize)
-    nj = batch.njets
-    rects = np.zeros(max(nj, 1), dtype=JET_RECT)
-    jet_offs = np.zeros(n + 1, dtype=np.int32)
-    if nj:
-        by_img = np.argsort(batch.jet_image, kind="stable")
-        rects["pix"][:nj] = pix_off[by_img]
-        rects["size"][:nj] = sizes[by_img]
-        rects["row0"][:nj] = batch.jet_row0[by_img]
-        rects["col0"][:nj] = batch.jet_col0[by_img]
-        jet_offs[1:] = np.cumsum(np.bincount(batch.jet_image, minlength=n))
-    total = batch.src_params.shape[0]
-    need = C.c_size_t(0)
-    L.check(lib.rsb_survey_workspace_bytes(n, size, total, C.byref(need)))
-    dt = np.float64 if f64 else np.float32
-    d_src = L.dev_from(batch.src_params if total else np.zeros((1, 6)))
-    d_offs = L.dev_from(batch.src_offs)
-    d_rects = L.dev_from(rects)
-    d_joffs = L.dev_from(jet_offs)
-    d_w = L.DeviceBuffer(need.value)
-    d_x = L.DeviceBuffer(n * size * size * np.dtype(dt).itemsize)
-    d_y = L.DeviceBuffer(n * 4 * size * size * np.dtype(dt).itemsize)
-    L.check(lib.rsb_survey_render(d_src.ptr, d_offs.ptr, total, d_rects.ptr, d_joffs.ptr, d_pix.ptr,
-                                  n, size, L.JET_OUT_F64 if f64 else 0, d_x.ptr, d_y.ptr, d_w.ptr,
-                                  d_w.nbytes, None), "rsb_survey_render")
-    x = d_x.download((n, 1, size, size), dt, pinned=True)
-    y = d_y.download((n, 4, size, size), dt, pinned=True)
-    return x, y
+    dev = DeviceSurvey(batch, jet_normalize, f64)
+    dev.enqueue()
+    return dev.download()
 
 
 def create_survey(grid, conf):

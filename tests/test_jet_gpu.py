@@ -47,7 +47,9 @@ def test_create_jet_matches_reference_golden(golden_dir, name):
 
 @pytest.mark.parametrize("size,n,seed,f64", [
     (128, 40, 21, True), (64, 30, 22, False), (101, 12, 23, True), (150, 12, 24, False),
-    (256, 24, 25, False), (300, 6, 26, True), (66, 10, 27, True)])
+    (256, 24, 25, False), (300, 6, 26, True), (66, 10, 27, True),
+    # odd sizes above 128: two CTAs per image with uneven bands (ceil / floor of N/2 rows)
+    (151, 12, 28, False), (199, 10, 29, True), (255, 8, 30, False), (130, 8, 31, False)])
 def test_render_matches_oracle(size, n, seed, f64):
     """Same seed -> same parameters -> images within 1e-5 of peak, margins exact."""
     from oracle import jet as ojet
@@ -174,3 +176,45 @@ def test_pipelined_create_jet_equals_single_shot():
     assert end_a == end_b
     assert x.shape == (n, 1, size, size) and np.array_equal(x[:, 0], img)
     assert np.array_equal(y, source_lists(b, margin, peak, True))
+
+
+def test_variable_size_launch_matches_oracle():
+    """rsb_jet_render_var: jets of many sizes (the sub-jets of a 1024^2 survey: 100..199 px, plus
+    small and 256 px ones) in one launch per cluster shape, each against the oracle."""
+    import ctypes as C
+
+    from oracle import jet as ojet
+    from radiosim_b200 import _lib as L
+    from radiosim_b200.jets.packer import pack_jets
+
+    L.require_device()
+    lib = L.lib()
+    rng = np.random.default_rng(5)
+    for sizes in (np.sort(rng.integers(100, 200, size=70)), np.array([8, 31, 64, 100, 101, 127, 128]),
+                  np.array([129, 130, 131, 197, 199, 200, 255, 256, 256])):
+        n = len(sizes)
+        refs, margins, peaks, params, zpads = [], [], [], [], []
+        for k, sz in enumerate(sizes):
+            np.random.seed(1000 + k)
+            trace = []
+            ox, _ = ojet.create_jet((1, 3, int(sz), int(sz)), (3, 10), "normalize", "clean", trace=trace)
+            np.random.seed(1000 + k)
+            b = pack_jets(1, int(sz), (3, 10), "normalize")
+            refs.append(ox[0, 0]); margins.append(trace[0]["margin"]); peaks.append(trace[0]["jet_max"])
+            params.append(b.params[0]); zpads.append(b.zoom_pad[0])
+        pitch = (sizes + 3) & ~3
+        offs = np.zeros(n, dtype=np.int64)
+        offs[1:] = np.cumsum(sizes * pitch)[:-1]
+        total = int((sizes * pitch).sum())
+        d_p, d_z = L.dev_from(np.array(params)), L.dev_from(np.array(zpads, dtype=np.int32))
+        d_s, d_o = L.dev_from(sizes.astype(np.int32)), L.dev_from(offs)
+        d_img, d_m, d_k = L.DeviceBuffer(total * 4), L.DeviceBuffer(n * 4), L.DeviceBuffer(n * 8)
+        L.check(lib.rsb_jet_render_var(d_p.ptr, d_z.ptr, d_s.ptr, d_o.ptr, n, 19, int(sizes.max()),
+                                       L.JET_NORMALIZE, d_img.ptr, d_m.ptr, d_k.ptr, None), "rsb_jet_render_var")
+        L.device_sync()
+        flat = d_img.download((total,), np.float32)
+        assert np.array_equal(d_m.download((n,), np.int32), np.array(margins))
+        assert np.allclose(d_k.download((n,), np.float64), np.array(peaks), rtol=1e-6, atol=0)
+        for k, sz in enumerate(sizes):
+            img = flat[offs[k] : offs[k] + sz * pitch[k]].reshape(sz, pitch[k])[:, :sz]
+            assert np.abs(img.astype(np.float64) - refs[k]).max() <= TOL_IMG, (int(sz), k)
