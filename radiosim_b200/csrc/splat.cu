@@ -36,11 +36,13 @@ namespace splat {
 constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
 constexpr int kTileRows = 64, kTileCols = 128;   // CTA tile
-constexpr int kSubRows = 4, kSubCols = 64;       // warp task: 4 rows x 64 columns, 2 columns per lane
-constexpr int kGroups = kTileRows / kSubRows;    // 16 row groups
+constexpr int kSubRows = 8, kSubCols = 64;       // warp task: 8 rows x 64 columns, 2 columns per lane
+constexpr int kGroups = kTileRows / kSubRows;    // 8 row groups
 constexpr int kHalves = kTileCols / kSubCols;    // 2
-constexpr int kSrcTasks = 2 * kGroups * kHalves; // class (wide, narrow) x group x half = 64
-constexpr int kRectTasks = kGroups * kHalves;    // 32
+constexpr int kSub = kGroups * kHalves;          // 16 sub-tiles = one per warp
+constexpr int kSrcTasks = 2 * kSub;              // class (wide, narrow) x sub-tile
+constexpr int kRectTasks = kSub;
+static_assert(kSub == kWarps, "one wide task per warp");
 constexpr int kRecCap = 512;                     // staged source records per round (24 KB)
 constexpr int kRectCap = 128;                    // staged sub-jet rectangles per round
 constexpr int kTilePx = kTileRows * kTileCols;
@@ -122,9 +124,13 @@ struct TileArgs {
   unsigned* peak;            // [n] float bits of max(sum of planes), zero-initialised
   unsigned* arrived;         // [n] tiles of the image whose maximum is in `peak`, zero-initialised
   unsigned* ticket;          // [1] next tile, zero-initialised
+  const int* order;          // [n][tiles] ticket -> tile of its image, most expensive tiles first
   void* out_x;               // [n][N][N]
   void* out_y;               // [n][4][N][N]
   int n, N, tiles_x, tiles;  // tiles per image row / per image
+  int direct;                // images with more tiles than the grid has CTAs cannot be held on chip
+                             // until their maximum is known: tiles are written unnormalised at
+                             // once (background plane = image) and norm_inplace_kernel finishes
 };
 
 struct ListInfo {            // one round of one tile, as the builder leaves it
@@ -202,13 +208,34 @@ __device__ inline void build_round(const TileArgs& a, int ticket, int s_begin, i
   }
 }
 
-// take the next ticket and build the first round of its list (one warp)
+// Take the next ticket and build the first round of its list (one warp).
+// A CTA holds a finished tile (waiting for its image's maximum) while it renders the next one.
+// It must never hold, at the same time, an UNRENDERED ticket of the image that finished tile
+// waits for -- it would wait for itself.  So a ticket of image `avoid_img` is not taken here
+// (kDeferred); the caller takes it once the finished tile has been flushed.  With that rule and
+// tiles per image <= CTAs of the grid no set of CTAs can wait on each other: the lowest
+// incomplete image's unrendered tickets are held by CTAs whose finished tile lies in a lower,
+// complete image, and if some of its tickets are still untaken, not every CTA can hold two of
+// its tiles.
+constexpr int kDeferred = -2;
 __device__ inline void build_next(const TileArgs& a, unsigned* list, unsigned* rlist, ListInfo* info,
-                                  int lane) {
+                                  int lane, int avoid_img) {
+  const int total = a.n * a.tiles;
   int t = 0;
-  if (lane == 0) t = (int)atomicAdd(a.ticket, 1u);
+  if (lane == 0) {
+    // The counter only grows and avoid_img is the image of a ticket this CTA already holds, so
+    // once the counter has left that image no later ticket can fall into it: a plain read
+    // decides, then atomicAdd takes whatever ticket is next.
+    bool defer = false;
+    if (avoid_img >= 0) {
+      const unsigned seen = *(volatile unsigned*)a.ticket;
+      defer = (int)seen < total && (int)(seen / (unsigned)a.tiles) == avoid_img;
+    }
+    t = defer ? kDeferred : (int)atomicAdd(a.ticket, 1u);
+    if (t > total) t = total;
+  }
   t = __shfl_sync(0xffffffffu, t, 0);
-  if (t >= a.n * a.tiles) {
+  if (t >= total || t == kDeferred) {
     if (lane == 0) {
       ListInfo li;
       li.ticket = t; li.nsrc = li.nwide = li.nrect = 0; li.src_resume = li.rect_resume = -1;
@@ -217,42 +244,48 @@ __device__ inline void build_next(const TileArgs& a, unsigned* list, unsigned* r
     }
     return;
   }
-  const int img = t / a.tiles, tile = t - img * a.tiles;
+  const int img = t / a.tiles, tile = a.order[t];
   const int ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
   build_round(a, t, a.offs[img * 3], a.offs[img * 3 + 1], a.offs[img * 3 + 2], a.jet_offs[img],
               a.jet_offs[img + 1], ty * kTileRows, tx * kTileCols, list, rlist, info, lane);
 }
 
-// ---- one source over this lane's 4 x 2 pixels ---------------------------------------------
+// ---- one source over this lane's 8 x 2 pixels ---------------------------------------------
 __device__ __forceinline__ void source_math(const float4& cq, const float4& cc, const float2& ck,
                                             float r0f, float c0f, f2 (&acc)[kSubRows]) {
   const float d0 = (c0f - cc.z) - cc.w;
   const f2 d = f2_pack(d0, d0 + 1.f);
   const f2 Q = f2_mul(f2_pack(cq.y, cq.y), d);
-  const float dr = (r0f - cc.x) - cc.y;
+  const float dr0 = (r0f - cc.x) - cc.y;
   if (ck.x > 0.f) {
+    // rows in two blocks of four, two exponentials per column and block (see Rec)
     const f2 Pq = f2_fma(f2_mul(f2_pack(cq.x, cq.x), d), d, f2_pack(cq.w, cq.w));  // A dc^2 + la
-    const float k2s = ck.x, k3s = ck.x * ck.x * ck.x;
-    const float Cq = cq.z * dr * dr;
-    const float tw = fmaf(2.f * cq.z, dr, cq.z);  // 2 C dr + C
-    float ta, tb, wa, wb;
-    f2_unpack(f2_fma(f2_pack(dr, dr), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
-    f2_unpack(f2_add(Q, f2_pack(tw, tw)), wa, wb);
-    // (the clamp never binds where the block holds a pixel above the cut-off; it keeps U^3 finite)
-    const f2 E0 = f2_pack(ex2(ta), ex2(tb));
-    const f2 U = f2_pack(ex2(fminf(wa, 40.f)), ex2(fminf(wb, 40.f)));
-    const f2 U2 = f2_mul(U, U);
-    acc[0] = f2_add(acc[0], E0);
-    acc[1] = f2_fma(E0, U, acc[1]);
-    acc[2] = f2_fma(E0, f2_mul(U2, f2_pack(k2s, k2s)), acc[2]);
-    acc[3] = f2_fma(E0, f2_mul(f2_mul(U2, U), f2_pack(k3s, k3s)), acc[3]);
+    const float k3s = ck.x * ck.x * ck.x;
+    const f2 k2 = f2_pack(ck.x, ck.x), k3 = f2_pack(k3s, k3s);
+#pragma unroll
+    for (int b = 0; b < kSubRows; b += 4) {
+      const float dr = dr0 + (float)b;
+      const float Cq = cq.z * dr * dr;
+      const float tw = fmaf(2.f * cq.z, dr, cq.z);  // 2 C dr + C
+      float ta, tb, wa, wb;
+      f2_unpack(f2_fma(f2_pack(dr, dr), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
+      f2_unpack(f2_add(Q, f2_pack(tw, tw)), wa, wb);
+      // (the clamp never binds where the block holds a pixel above the cut-off; it keeps U^3 finite)
+      const f2 E0 = f2_pack(ex2(ta), ex2(tb));
+      const f2 U = f2_pack(ex2(fminf(wa, 40.f)), ex2(fminf(wb, 40.f)));
+      const f2 U2 = f2_mul(U, U);
+      acc[b] = f2_add(acc[b], E0);
+      acc[b + 1] = f2_fma(E0, U, acc[b + 1]);
+      acc[b + 2] = f2_fma(E0, f2_mul(U2, k2), acc[b + 2]);
+      acc[b + 3] = f2_fma(E0, f2_mul(f2_mul(U2, U), k3), acc[b + 3]);
+    }
   } else {
     // one exponential per pixel; cq.w holds the amplitude itself
     const f2 Pq = f2_mul(f2_mul(f2_pack(cq.x, cq.x), d), d);
     const f2 amp2 = f2_pack(cq.w, cq.w);
 #pragma unroll
     for (int i = 0; i < kSubRows; ++i) {
-      const float dri = dr + (float)i;
+      const float dri = dr0 + (float)i;
       const float Cq = cq.z * dri * dri;
       float ta, tb;
       f2_unpack(f2_fma(f2_pack(dri, dri), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
@@ -291,17 +324,20 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
 
   // scale and write a finished tile once its image's maximum is final
   auto flush = [&](int ticket, int pb) {
-    const int img = ticket / a.tiles, tile = ticket - img * a.tiles;
+    const int img = ticket / a.tiles, tile = a.order[ticket];
     const int ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
     const int R0 = ty * kTileRows, C0 = tx * kTileCols;
-    if (tid == 0) {
-      volatile unsigned* arr = a.arrived + img;
-      while (*arr < (unsigned)a.tiles) __nanosleep(64);
-      __threadfence();
-      sm.inv = 1.f / __uint_as_float(*(volatile unsigned*)(a.peak + img));
+    float inv = 1.f;
+    if (!a.direct) {
+      if (tid == 0) {
+        volatile unsigned* arr = a.arrived + img;
+        while (*arr < (unsigned)a.tiles) __nanosleep(64);
+        __threadfence();
+        sm.inv = 1.f / __uint_as_float(*(volatile unsigned*)(a.peak + img));
+      }
+      __syncthreads();
+      inv = sm.inv;
     }
-    __syncthreads();
-    const float inv = sm.inv;
     OutT* x = reinterpret_cast<OutT*>(a.out_x) + (size_t)img * npx;
     OutT* y = reinterpret_cast<OutT*>(a.out_y) + (size_t)img * 4 * npx;
     const float* p0 = sm.plane[pb][0];
@@ -321,19 +357,20 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
       store4(y + o, vec, valid, make_float4(a0.x * inv, a0.y * inv, a0.z * inv, a0.w * inv));
       store4(y + npx + o, vec, valid, make_float4(a1.x * inv, a1.y * inv, a1.z * inv, a1.w * inv));
       store4(y + 2 * npx + o, vec, valid, make_float4(a2.x * inv, a2.y * inv, a2.z * inv, a2.w * inv));
-      store4(y + 3 * npx + o, vec, valid, make_float4(1.f - s.x, 1.f - s.y, 1.f - s.z, 1.f - s.w));
+      if (!a.direct)
+        store4(y + 3 * npx + o, vec, valid, make_float4(1.f - s.x, 1.f - s.y, 1.f - s.z, 1.f - s.w));
     }
   };
 
-  if (warp == kBuilderWarp) build_next(a, sm.list[0], sm.rlist[0], &sm.info[0], lane);
+  if (warp == kBuilderWarp) build_next(a, sm.list[0], sm.rlist[0], &sm.info[0], lane, -1);
   __syncthreads();
 
   int lb = 0, pb = 0;      // list buffer / plane buffer of the current tile
   int prev_ticket = -1;    // finished tile waiting in plane buffer pb ^ 1
   for (;;) {
     ListInfo li = sm.info[lb];
-    if (li.ticket >= total_tiles) break;
-    const int img = li.ticket / a.tiles, tile = li.ticket - img * a.tiles;
+    if (li.ticket >= total_tiles) break;  // (a deferred ticket was replaced before the loop turned)
+    const int img = li.ticket / a.tiles, tile = a.order[li.ticket];
     const int ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
     const int R0 = ty * kTileRows, C0 = tx * kTileCols;
     const int o2 = a.offs[img * 3 + 1], o3 = a.offs[img * 3 + 2], j1 = a.jet_offs[img + 1];
@@ -361,17 +398,22 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
       // the builder warp prepares the next tile while the others render this one
       const bool last_round = li.src_resume < 0 && li.rect_resume < 0;
       if (warp == kBuilderWarp && last_round)
-        build_next(a, sm.list[lb ^ 1], sm.rlist[lb ^ 1], &sm.info[lb ^ 1], lane);
+        build_next(a, sm.list[lb ^ 1], sm.rlist[lb ^ 1], &sm.info[lb ^ 1], lane,
+                   (prev_ticket >= 0 && !a.direct) ? prev_ticket / a.tiles : -1);
 
       // ---- tasks ---------------------------------------------------------------------------
-      for (;;) {
+      // 48 tasks: class (wide, narrow, sub-jets) x sub-tile.  The wide class is most of the work
+      // and spreads evenly over a tile (footprints of hundreds of pixels), so every warp takes
+      // the wide task of its own sub-tile; the other 32 tasks are handed out by a counter.
+      auto next_task = [&]() -> int {
         int t = 0;
-        if (lane == 0) t = atomicAdd(&sm.task, 1);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= kSrcTasks + kRectTasks) break;
+        if (lane == 0) t = kSub + atomicAdd(&sm.task, 1);
+        return __shfl_sync(0xffffffffu, t, 0);
+      };
+      for (int t = warp; t < 3 * kSub; t = next_task()) {
         const bool is_src = t < kSrcTasks;
-        const int u = is_src ? (t & (kSrcTasks / 2 - 1)) : t - kSrcTasks;
-        const int cls = is_src ? (t >> 5) : 0;            // 0: wide, 1: narrow
+        const int cls = t >= kSub ? 1 : 0;                // 0: wide, 1: narrow
+        const int u = t & (kSub - 1);
         const int g = u >> 1, half = u & 1;
         const int lo = is_src ? (cls ? li.nwide : 0) : 0;
         const int hi = is_src ? (cls ? li.nsrc : li.nwide) : li.nrect;
@@ -410,52 +452,75 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
               }
               unsigned hits = __ballot_sync(0xffffffffu, hit);
               if (!hits) continue;
-              // coefficients of the hit about to be rendered; the next hit's are requested
-              // before this one's arithmetic
-              const Rec* rk = &sm.rec[k0 + lowest_bit(hits)];
-              float4 q = *reinterpret_cast<const float4*>(&rk->A);
-              float4 ct = *reinterpret_cast<const float4*>(&rk->irf);
-              float2 kk = *reinterpret_cast<const float2*>(&rk->k2);
-              while (hits) {
+              // Coefficients of the hit about to be rendered; the next hit's are requested before
+              // this one's arithmetic (the warp barrier keeps the loads above it).  Unrolled by
+              // two so that the two coefficient sets swap roles without register moves.
+              auto fetch = [&](int b, float4& q_, float4& c_, float2& k_) {
+                const Rec* rn = &sm.rec[k0 + max(b, 0)];
+                q_ = *reinterpret_cast<const float4*>(&rn->A);
+                c_ = *reinterpret_cast<const float4*>(&rn->irf);
+                k_ = *reinterpret_cast<const float2*>(&rn->k2);
+              };
+              float4 q, ct, qb, cb2;
+              float2 kk, kb;
+              fetch(lowest_bit(hits), q, ct, kk);
+              for (;;) {
                 hits &= hits - 1;
-                const Rec* rn = &sm.rec[k0 + max(lowest_bit(hits), 0)];
-                const float4 qn = *reinterpret_cast<const float4*>(&rn->A);
-                const float4 cn = *reinterpret_cast<const float4*>(&rn->irf);
-                const float2 kn = *reinterpret_cast<const float2*>(&rn->k2);
+                fetch(lowest_bit(hits), qb, cb2, kb);
                 __syncwarp();
                 source_math(q, ct, kk, r0f, c0f, acc);
-                q = qn; ct = cn; kk = kn;
+                if (!hits) break;
+                hits &= hits - 1;
+                fetch(lowest_bit(hits), q, ct, kk);
+                __syncwarp();
+                source_math(qb, cb2, kb, r0f, c0f, acc);
+                if (!hits) break;
               }
             }
           } else {
-            // class 0: paste the sub-jets that overlap the task's rectangle (survey.py:61-76)
+            // class 0: paste the sub-jets that overlap the task's rectangle (survey.py:61-76).
+            // Branch-free gathers from clamped addresses (16 independent loads per hit, masked
+            // afterwards), and the next hit's loads are issued before this hit's additions.
             float a0[kSubRows], a1[kSubRows];
 #pragma unroll
             for (int i = 0; i < kSubRows; ++i) a0[i] = a1[i] = 0.f;
             for (int k0 = 0; k0 < hi; k0 += 32) {
               bool hit = false;
-              JetRect jr;
-              jr.pix = 0; jr.size = jr.row0 = jr.col0 = jr.pitch = 0;
               if (k0 + lane < hi) {
-                jr = sm.rect[k0 + lane];
+                const JetRect jr = sm.rect[k0 + lane];
                 hit = !(jr.row0 > r0 + kSubRows - 1 || jr.row0 + jr.size <= r0 ||
                         jr.col0 > c0t + kSubCols - 1 || jr.col0 + jr.size <= c0t);
               }
               unsigned hits = __ballot_sync(0xffffffffu, hit);
-              while (hits) {
-                const int src = lowest_bit(hits);
-                hits &= hits - 1;
-                const JetRect h = sm.rect[k0 + src];
+              if (!hits) continue;
+              float v0[kSubRows], v1[kSubRows];   // pixels of the hit in flight
+              int fr = 0, fc = 0, fs = 0;         // ... its first row / column relative to the task, its size
+              auto gather = [&](int b) {
+                const JetRect h = sm.rect[k0 + max(b, 0)];
                 const float* jp = a.jet_pix + h.pix;
-                const int jc = c0 - h.col0;
-                const bool in0 = jc >= 0 && jc < h.size, in1 = jc + 1 >= 0 && jc + 1 < h.size;
+                fr = r0 - h.row0; fc = c0 - h.col0; fs = h.size;
+                const int jc0 = min(max(fc, 0), fs - 1), jc1 = min(max(fc + 1, 0), fs - 1);
 #pragma unroll
                 for (int i = 0; i < kSubRows; ++i) {
-                  const int ji = r0 + i - h.row0;
-                  if (ji >= 0 && ji < h.size) {
-                    if (in0) a0[i] += __ldg(jp + (size_t)ji * h.pitch + jc);
-                    if (in1) a1[i] += __ldg(jp + (size_t)ji * h.pitch + jc + 1);
-                  }
+                  const float* rowp = jp + (size_t)min(max(fr + i, 0), fs - 1) * h.pitch;
+                  v0[i] = __ldg(rowp + jc0);
+                  v1[i] = __ldg(rowp + jc1);
+                }
+              };
+              gather(lowest_bit(hits));
+              while (hits) {
+                hits &= hits - 1;
+                float w0[kSubRows], w1[kSubRows];
+                const int gr = fr, gc = fc, gs = fs;
+#pragma unroll
+                for (int i = 0; i < kSubRows; ++i) { w0[i] = v0[i]; w1[i] = v1[i]; }
+                if (hits) gather(lowest_bit(hits));   // (warp-uniform)
+                const bool in0 = gc >= 0 && gc < gs, in1 = gc + 1 >= 0 && gc + 1 < gs;
+#pragma unroll
+                for (int i = 0; i < kSubRows; ++i) {
+                  const bool rin = gr + i >= 0 && gr + i < gs;
+                  a0[i] += (rin && in0) ? w0[i] : 0.f;
+                  a1[i] += (rin && in1) ? w1[i] : 0.f;
                 }
               }
             }
@@ -511,14 +576,96 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
         atomicAdd(a.arrived + img, 1u);
       }
     }
+    if (a.direct) {
+      __syncthreads();
+      flush(li.ticket, pb);
+      __syncthreads();  // the planes are free again; the next tile's list is visible
+      lb ^= 1;
+      continue;
+    }
     // ---- flush the tile finished one step ago (its image has had a whole tile time) --------
     if (prev_ticket >= 0) flush(prev_ticket, pb ^ 1);
     prev_ticket = li.ticket;
     pb ^= 1;
     lb ^= 1;
     __syncthreads();  // the next tile's list (builder warp) is visible; buffers swapped
+    if (sm.info[lb].ticket == kDeferred) {  // (uniform) the ticket the builder had to leave alone
+      __syncthreads();
+      if (warp == kBuilderWarp) build_next(a, sm.list[lb], sm.rlist[lb], &sm.info[lb], lane, -1);
+      __syncthreads();
+    }
   }
-  if (prev_ticket >= 0) flush(prev_ticket, pb ^ 1);
+  if (prev_ticket >= 0 && !a.direct) flush(prev_ticket, pb ^ 1);
+}
+
+// ---- tile order: most expensive tiles of an image first ------------------------------------
+// An image is complete (its maximum final, its tiles free to leave the chip) when its LAST
+// tile is done; handing out the cheap border tiles last keeps that moment close to the last
+// ticket.  Cost proxy: pixels of the tile inside the sources' boxes (+ a quarter for pasted
+// sub-jet pixels).  One warp per tile.
+__global__ void __launch_bounds__(128) cost_kernel(const TileArgs a, unsigned* __restrict__ cost) {
+  const int lane = threadIdx.x & 31, tile = blockIdx.x * 4 + (threadIdx.x >> 5), img = blockIdx.y;
+  if (tile >= a.tiles) return;
+  const int ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
+  const int R0 = ty * kTileRows, C0 = tx * kTileCols, R1 = R0 + kTileRows - 1, C1 = C0 + kTileCols - 1;
+  const int o1 = a.offs[img * 3], o3 = a.offs[img * 3 + 2];
+  unsigned sum = 0u;
+  for (int s = o1 + lane; s < o3; s += 32) {
+    const int4 bb = a.bbox[s];
+    const int h = min(bb.y, R1) - max(bb.x, R0) + 1, w = min(bb.w, C1) - max(bb.z, C0) + 1;
+    if (h > 0 && w > 0) sum += (unsigned)(h * w);
+  }
+  unsigned rsum = 0u;
+  for (int j = a.jet_offs[img] + lane; j < a.jet_offs[img + 1]; j += 32) {
+    const JetRect jr = a.jets[j];
+    const int h = min(jr.row0 + jr.size - 1, R1) - max(jr.row0, R0) + 1;
+    const int w = min(jr.col0 + jr.size - 1, C1) - max(jr.col0, C0) + 1;
+    if (h > 0 && w > 0) rsum += (unsigned)(h * w);
+  }
+  sum += rsum >> 2;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) cost[(size_t)img * a.tiles + tile] = sum;
+}
+
+// one CTA per image: order[rank] = tile, rank by descending cost (ties: tile index)
+__global__ void __launch_bounds__(256) order_kernel(const unsigned* __restrict__ cost, int tiles,
+                                                    int* __restrict__ order) {
+  extern __shared__ unsigned c_sm[];
+  const int img = blockIdx.x;
+  for (int j = threadIdx.x; j < tiles; j += blockDim.x) c_sm[j] = cost[(size_t)img * tiles + j];
+  __syncthreads();
+  for (int j = threadIdx.x; j < tiles; j += blockDim.x) {
+    const unsigned cj = c_sm[j];
+    int rank = 0;
+    for (int k = 0; k < tiles; ++k) rank += (c_sm[k] > cj || (c_sm[k] == cj && k < j)) ? 1 : 0;
+    order[(size_t)img * tiles + rank] = j;
+  }
+}
+
+__global__ void identity_order_kernel(int tiles, size_t total, int* __restrict__ order) {
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x)
+    order[e] = (int)(e % (size_t)tiles);
+}
+
+// direct mode only: x *= 1/max, y[0..2] *= 1/max, y[3] = 1 - x, in place
+template <typename OutT>
+__global__ void __launch_bounds__(256) norm_inplace_kernel(const unsigned* __restrict__ peak, int N,
+                                                           OutT* __restrict__ out_x, OutT* __restrict__ out_y) {
+  const size_t npx = (size_t)N * N;
+  const int img = blockIdx.y;
+  const float inv = 1.f / __uint_as_float(peak[img]);
+  OutT* x = out_x + (size_t)img * npx;
+  OutT* y = out_y + (size_t)img * 4 * npx;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < npx; e += (size_t)gridDim.x * blockDim.x) {
+    const float a0 = (float)y[e], a1 = (float)y[npx + e], a2 = (float)y[2 * npx + e];
+    const float s = ((a0 + a1) + a2) * inv;
+    x[e] = (OutT)s;
+    y[e] = (OutT)(a0 * inv);
+    y[npx + e] = (OutT)(a1 * inv);
+    y[2 * npx + e] = (OutT)(a2 * inv);
+    y[3 * npx + e] = (OutT)(1.f - s);
+  }
 }
 
 }  // namespace splat
@@ -535,8 +682,9 @@ int rsb_survey_workspace_bytes(int n, int size, int total_sources, size_t* bytes
   RSB_ARG(bytes != nullptr && n >= 0 && size >= 2 && total_sources >= 0,
           "rsb_survey_workspace_bytes: bad arguments");
   const size_t s = (size_t)(total_sources > 0 ? total_sources : 1);
+  const size_t tiles = (size_t)((size + kTileCols - 1) / kTileCols) * ((size + kTileRows - 1) / kTileRows);
   *bytes = align256((2 * (size_t)n + 1) * sizeof(unsigned)) + align256(s * sizeof(Rec)) +
-           align256(s * sizeof(int4));
+           align256(s * sizeof(int4)) + 2 * align256((size_t)n * tiles * sizeof(unsigned));
   return 0;
 }
 
@@ -562,6 +710,11 @@ int rsb_survey_render(const double* src_params, const int32_t* src_offs, int tot
   Rec* rec = (Rec*)(w + off);
   off += align256((size_t)(total_sources > 0 ? total_sources : 1) * sizeof(Rec));
   int4* bbox = (int4*)(w + off);
+  off += align256((size_t)(total_sources > 0 ? total_sources : 1) * sizeof(int4));
+  const size_t ntile = (size_t)n * tiles_x * tiles_y;
+  unsigned* cost = (unsigned*)(w + off);
+  off += align256(ntile * sizeof(unsigned));
+  int* order = (int*)(w + off);
   RSB_CUDA(cudaMemsetAsync(ctl, 0, ctl_bytes, st));
   if (total_sources > 0) {
     // tau: 1e-9 of the largest amplitude any source can have (amp ~ U(0,1), sub-jets peak at 1)
@@ -575,6 +728,17 @@ int rsb_survey_render(const double* src_params, const int32_t* src_offs, int tot
   const size_t smem = sizeof(Smem);
   int grid = sm_count();
   if ((long long)grid > (long long)n * a.tiles) grid = n * a.tiles;
+  a.direct = a.tiles > grid ? 1 : 0;
+  a.order = order;
+  if (a.direct) {
+    identity_order_kernel<<<64, 256, 0, st>>>(a.tiles, ntile, order);
+    RSB_LAUNCHED();
+  } else {
+    cost_kernel<<<dim3((a.tiles + 3) / 4, n), 128, 0, st>>>(a, cost);
+    RSB_LAUNCHED();
+    order_kernel<<<n, 256, (size_t)a.tiles * sizeof(unsigned), st>>>(cost, a.tiles, order);
+    RSB_LAUNCHED();
+  }
   if (flags & RSB_JET_OUT_F64) {
     RSB_CUDA(cudaFuncSetAttribute(tile_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     tile_kernel<double><<<grid, kThreads, smem, st>>>(a);
@@ -583,6 +747,21 @@ int rsb_survey_render(const double* src_params, const int32_t* src_offs, int tot
     tile_kernel<float><<<grid, kThreads, smem, st>>>(a);
   }
   RSB_LAUNCHED();
+  if (a.direct) {
+    int bx = (int)(((size_t)size * size + 255) / 256);
+    if (bx > 2048) bx = 2048;
+    for (int i0 = 0; i0 < n; i0 += 65535) {
+      const int cnt = (n - i0) < 65535 ? (n - i0) : 65535;
+      const size_t px = (size_t)size * size;
+      if (flags & RSB_JET_OUT_F64)
+        norm_inplace_kernel<double><<<dim3(bx, cnt), 256, 0, st>>>(a.peak + i0, size, (double*)out_x + i0 * px,
+                                                                   (double*)out_y + (size_t)i0 * 4 * px);
+      else
+        norm_inplace_kernel<float><<<dim3(bx, cnt), 256, 0, st>>>(a.peak + i0, size, (float*)out_x + i0 * px,
+                                                                  (float*)out_y + (size_t)i0 * 4 * px);
+      RSB_LAUNCHED();
+    }
+  }
   return 0;
 }
 
