@@ -114,6 +114,7 @@ def require_device() -> None:
 
 def set_device(dev: int) -> None:
     check(_lib.rsb_set_device(int(dev)), "rsb_set_device")
+    _CUR_DEV[0] = int(dev)
 
 
 def launch_count() -> int:
@@ -126,18 +127,61 @@ def device_sync() -> None:
     check(_lib.rsb_device_sync(), "rsb_device_sync")
 
 
+# cudaMalloc / cudaFree cost ~0.1 ms each and synchronise the device; the drop-in functions need a
+# dozen small buffers per call, so freed blocks are kept (per device, by size class) for the next
+# call -- up to RSB_DEVICE_POOL_MB (default 8192) in total.
+_DPOOL: dict = {}         # (device, size class) -> [ptr]
+_DPOOL_BYTES = [0]
+_DPOOL_CAP = int(os.environ.get("RSB_DEVICE_POOL_MB", "8192")) << 20
+_CUR_DEV = [0]
+
+
+def _size_class(nbytes: int) -> int:
+    """Allocation size for a request: powers of two up to 1 MiB, then multiples of 1/8 of the
+    power of two below (at most 12.5 % over-allocation)."""
+    n = max(int(nbytes), 256)
+    if n <= (1 << 20):
+        return 1 << (n - 1).bit_length()
+    step = 1 << ((n - 1).bit_length() - 4)
+    return -(-n // step) * step
+
+
+def device_pool_clear() -> None:
+    """Return every cached device block to the driver."""
+    for ptrs in _DPOOL.values():
+        for ptr in ptrs:
+            _lib.rsb_free(ptr)
+    _DPOOL.clear()
+    _DPOOL_BYTES[0] = 0
+
+
 class DeviceBuffer:
-    """Owning handle of a device allocation (rsb_malloc / rsb_free)."""
+    """Owning handle of a device allocation (rsb_malloc / rsb_free, pooled)."""
 
     def __init__(self, nbytes: int):
-        p = _vp()
-        check(_lib.rsb_malloc(C.byref(p), int(nbytes)), "rsb_malloc")
-        self.ptr = p.value
         self.nbytes = int(nbytes)
+        self._cls = _size_class(nbytes)
+        self._dev = _CUR_DEV[0]
+        free = _DPOOL.get((self._dev, self._cls))
+        if free:
+            self.ptr = free.pop()
+            _DPOOL_BYTES[0] -= self._cls
+            return
+        p = _vp()
+        rc = _lib.rsb_malloc(C.byref(p), self._cls)
+        if rc != 0 and _DPOOL:      # out of memory with blocks cached: give them back and retry
+            device_pool_clear()
+            rc = _lib.rsb_malloc(C.byref(p), self._cls)
+        check(rc, "rsb_malloc")
+        self.ptr = p.value
 
     def free(self):
         if getattr(self, "ptr", None):
-            _lib.rsb_free(self.ptr)
+            if _DPOOL_BYTES[0] + self._cls <= _DPOOL_CAP:
+                _DPOOL.setdefault((self._dev, self._cls), []).append(self.ptr)
+                _DPOOL_BYTES[0] += self._cls
+            else:
+                _lib.rsb_free(self.ptr)
             self.ptr = None
 
     def __del__(self):
@@ -223,6 +267,25 @@ def pinned_empty(shape, dtype) -> np.ndarray:
     buf = (C.c_char * max(nbytes, 1)).from_address(owner.ptr)
     buf._rsb_owner = owner
     return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+
+def upload_blob(arrays):
+    """Several small host arrays -> ONE page-locked staging block, one device block and one
+    asynchronous copy on the default stream.  Returns ``(device buffer, [device pointers], staging
+    array)``; keep the staging array alive until the stream has passed the copy."""
+    arrays = [np.ascontiguousarray(a) for a in arrays]
+    offs, total = [], 0
+    for a in arrays:
+        offs.append(total)
+        total += (a.nbytes + 255) & ~255
+    total = max(total, 256)
+    stage = pinned_empty((total,), np.uint8)
+    for a, o in zip(arrays, offs):
+        if a.nbytes:
+            stage[o : o + a.nbytes] = a.reshape(-1).view(np.uint8)
+    buf = DeviceBuffer(total)
+    check(_lib.rsb_memcpy_h2d(buf.ptr, stage.ctypes.data, total, None), "h2d")
+    return buf, [buf.ptr + o for o in offs], stage
 
 
 def dev_from(arr: np.ndarray) -> DeviceBuffer:

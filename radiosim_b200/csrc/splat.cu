@@ -402,15 +402,17 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
                    (prev_ticket >= 0 && !a.direct) ? prev_ticket / a.tiles : -1);
 
       // ---- tasks ---------------------------------------------------------------------------
-      // 48 tasks: class (wide, narrow, sub-jets) x sub-tile.  The wide class is most of the work
-      // and spreads evenly over a tile (footprints of hundreds of pixels), so every warp takes
-      // the wide task of its own sub-tile; the other 32 tasks are handed out by a counter.
+      // 48 tasks: class (wide, narrow, sub-jets) x sub-tile, handed out by a counter.  Queue
+      // order: wide (exp-bound) and sub-jet (gather-latency-bound) tasks alternate, so both kinds
+      // are in flight on the SM at any time; the cheap narrow tasks come last and even out the end.
       auto next_task = [&]() -> int {
         int t = 0;
-        if (lane == 0) t = kSub + atomicAdd(&sm.task, 1);
+        if (lane == 0) t = atomicAdd(&sm.task, 1);
         return __shfl_sync(0xffffffffu, t, 0);
       };
-      for (int t = warp; t < 3 * kSub; t = next_task()) {
+      for (int q = next_task(); q < 3 * kSub; q = next_task()) {
+        // q -> task: [0, 32): even = wide, odd = sub-jets of sub-tile q/2; [32, 48): narrow
+        const int t = q < 2 * kSub ? ((q & 1) ? 2 * kSub + (q >> 1) : (q >> 1)) : q - kSub;
         const bool is_src = t < kSrcTasks;
         const int cls = t >= kSub ? 1 : 0;                // 0: wide, 1: narrow
         const int u = t & (kSub - 1);

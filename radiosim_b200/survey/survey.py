@@ -142,9 +142,10 @@ def pack_survey_py(n: int, size: int, num_sources: int, class_distribution, scal
 
 
 class DeviceSurvey:
-    """A packed batch resident on the device: everything is uploaded once, :meth:`enqueue` issues
-    the kernels (sub-jets in at most two variable-size launches, then ``rsb_survey_render``) on the
-    default stream without synchronising, :meth:`download` copies the two results to host arrays."""
+    """A packed batch resident on the device: everything is uploaded in one asynchronous copy,
+    :meth:`enqueue` issues the kernels (sub-jets in at most two variable-size launches, then
+    ``rsb_survey_render``) on the default stream without synchronising, :meth:`download` copies the
+    two results to host arrays."""
 
     def __init__(self, batch: SurveyBatch, jet_normalize: bool = True, f64: bool = True):
         L.require_device()
@@ -173,13 +174,6 @@ class DeviceSurvey:
                 raise L.RsbError("survey sub-jets larger than 256 pixels or with more than 32 slots "
                                  "are not supported by the variable-size jet launch")
         self.slots = all_params.shape[1] if nj else 1
-        self.d_pix = L.DeviceBuffer(max(total_pix * 4, 16))
-        if nj:
-            self.d_p = L.dev_from(all_params[order])
-            self.d_z = L.dev_from(all_zpad[order])
-            self.d_sizes = L.dev_from(ssz.astype(np.int32))
-            self.d_offs = L.dev_from(pix_sorted)
-            self.d_m, self.d_k = L.DeviceBuffer(nj * 4), L.DeviceBuffer(nj * 8)
         rects = np.zeros(max(nj, 1), dtype=JET_RECT)
         jet_offs = np.zeros(n + 1, dtype=np.int32)
         if nj:
@@ -197,10 +191,16 @@ class DeviceSurvey:
         need = C.c_size_t(0)
         L.check(self.lib.rsb_survey_workspace_bytes(n, size, self.total, C.byref(need)))
         self.dt = np.float64 if f64 else np.float32
-        self.d_src = L.dev_from(batch.src_params if self.total else np.zeros((1, 6)))
-        self.d_soffs = L.dev_from(batch.src_offs if n else np.zeros((1, 3), np.int32))
-        self.d_rects = L.dev_from(rects)
-        self.d_joffs = L.dev_from(jet_offs)
+        none = np.zeros(1)
+        self.d_in, ptrs, self._stage = L.upload_blob([
+            all_params[order] if nj else none, all_zpad[order] if nj else none,
+            ssz.astype(np.int32) if nj else none, pix_sorted if nj else none, rects, jet_offs,
+            batch.src_params if self.total else np.zeros((1, 6)),
+            batch.src_offs if n else np.zeros((1, 3), np.int32)])
+        (self.p_params, self.p_zpad, self.p_sizes, self.p_offs, self.p_rects, self.p_joffs,
+         self.p_src, self.p_soffs) = ptrs
+        self.d_pix = L.DeviceBuffer(max(total_pix * 4, 16))
+        self.d_mk = L.DeviceBuffer(max(nj, 1) * 12 + 256)     # margins and peaks of the sub-jets (unused here)
         self.d_w = L.DeviceBuffer(max(need.value, 16))
         esz = np.dtype(self.dt).itemsize
         self.d_x = L.DeviceBuffer(max(n * size * size * esz, 16))
@@ -208,22 +208,36 @@ class DeviceSurvey:
 
     def enqueue(self):
         lib = self.lib
+        p_margin = self.d_mk.ptr
+        p_peak = (self.d_mk.ptr + max(self.nj, 1) * 4 + 255) & ~255
         for a, b, max_size in self.groups:
-            L.check(lib.rsb_jet_render_var(self.d_p.ptr + a * self.slots * 48, self.d_z.ptr + a * 4,
-                                           self.d_sizes.ptr + a * 4, self.d_offs.ptr + a * 8, b - a,
+            L.check(lib.rsb_jet_render_var(self.p_params + a * self.slots * 48, self.p_zpad + a * 4,
+                                           self.p_sizes + a * 4, self.p_offs + a * 8, b - a,
                                            self.slots, max_size, self.flags_jet, self.d_pix.ptr,
-                                           self.d_m.ptr + a * 4, self.d_k.ptr + a * 8, None),
+                                           p_margin + a * 4, p_peak + a * 8, None),
                     "rsb_jet_render_var (survey sub-jets)")
         if self.n:
-            L.check(lib.rsb_survey_render(self.d_src.ptr, self.d_soffs.ptr, self.total, self.d_rects.ptr,
-                                          self.d_joffs.ptr, self.d_pix.ptr, self.n, self.size,
+            L.check(lib.rsb_survey_render(self.p_src, self.p_soffs, self.total, self.p_rects,
+                                          self.p_joffs, self.d_pix.ptr, self.n, self.size,
                                           L.JET_OUT_F64 if self.f64 else 0, self.d_x.ptr, self.d_y.ptr,
                                           self.d_w.ptr, self.d_w.nbytes, None), "rsb_survey_render")
 
+    def download_into(self, x: np.ndarray, y: np.ndarray):
+        """Asynchronous copies into (page-locked, contiguous) host arrays; ``L.device_sync()`` or a
+        later synchronising call completes them.  Keep this object alive until then."""
+        n, size = self.n, self.size
+        assert x.shape == (n, 1, size, size) and y.shape == (n, 4, size, size)
+        assert x.dtype == self.dt and y.dtype == self.dt and x.flags.c_contiguous and y.flags.c_contiguous
+        if n:
+            L.check(self.lib.rsb_memcpy_d2h(x.ctypes.data, self.d_x.ptr, x.nbytes, None), "d2h")
+            L.check(self.lib.rsb_memcpy_d2h(y.ctypes.data, self.d_y.ptr, y.nbytes, None), "d2h")
+
     def download(self):
         n, size = self.n, self.size
-        x = self.d_x.download((n, 1, size, size), self.dt, pinned=True)
-        y = self.d_y.download((n, 4, size, size), self.dt, pinned=True)
+        x = L.pinned_empty((n, 1, size, size), self.dt)
+        y = L.pinned_empty((n, 4, size, size), self.dt)
+        self.download_into(x, y)
+        L.device_sync()
         return x, y
 
 
@@ -233,11 +247,48 @@ def render_survey(batch: SurveyBatch, jet_normalize: bool = True, f64: bool = Tr
     return dev.download()
 
 
+def _chunk_images(n: int, size: int) -> int:
+    """Images per pipeline step: about 64 MB of float64 results."""
+    return max(1, min(n, (64 << 20) // (5 * size * size * 8)))
+
+
 def create_survey(grid, conf):
-    """Drop-in for ``radiosim.survey.create_survey``: ``(survey[n,1,N,N], comps[n,4,N,N])`` float64."""
+    """Drop-in for ``radiosim.survey.create_survey``: ``(survey[n,1,N,N], comps[n,4,N,N])`` float64.
+
+    The legacy RNG chain (sequential by nature) is drawn chunk after chunk on a helper thread while
+    the device renders the previous chunk and copies it to the host; the chunks are packed strictly
+    in order, so the global ``np.random`` stream is consumed exactly as by one pass."""
+    from concurrent.futures import ThreadPoolExecutor
+
     shape = tuple(grid.shape)
     n = 1 if len(shape) == 3 else shape[0]
     size = shape[-1]
-    batch = pack_survey(n, size, conf.survey.num_sources, conf.survey.class_distribution,
-                        conf.survey.scale_sources, conf.jet.num_jet_components, conf.jet.scaling)
-    return render_survey(batch, conf.jet.scaling == "normalize", f64=True)
+    sconf, jconf = conf.survey, conf.jet
+    args = (size, sconf.num_sources, sconf.class_distribution, sconf.scale_sources,
+            jconf.num_jet_components, jconf.scaling)
+    normalize = jconf.scaling == "normalize"
+    step = _chunk_images(n, size)
+    if n <= step:
+        return render_survey(pack_survey(n, *args), normalize, f64=True)
+    L.require_device()
+    x = L.pinned_empty((n, 1, size, size), np.float64)
+    y = L.pinned_empty((n, 4, size, size), np.float64)
+    in_flight = []
+    with ThreadPoolExecutor(1) as ex:
+        fut = ex.submit(pack_survey, min(step, n), *args)
+        i0 = 0
+        while i0 < n:
+            batch = fut.result()
+            i1 = i0 + batch.n
+            if i1 < n:
+                fut = ex.submit(pack_survey, min(step, n - i1), *args)
+            dev = DeviceSurvey(batch, normalize, f64=True)
+            dev.enqueue()
+            dev.download_into(x[i0:i1], y[i0:i1])
+            in_flight.append(dev)
+            if len(in_flight) > 2:      # bound the device memory held by unfinished chunks
+                L.device_sync()
+                in_flight.clear()
+            i0 = i1
+    L.device_sync()
+    return x, y
