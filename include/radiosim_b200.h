@@ -280,6 +280,31 @@ int rsb_survey_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, doubl
                     int32_t* jet_zoom_pad, int32_t* jet_size, int32_t* jet_image, int32_t* jet_row0,
                     int32_t* jet_col0, int32_t* njets_out);
 
+/* ---------------------------------------------------------------------- noise */
+/* add_noise, reference src/radiosim/utils/utils.py:259-315 (called from
+ * src/radiosim/simulations/simulations.py:101-108 for mojave bundles): a white field plus two
+ * Gaussian-filtered fields (scipy fftconvolve with astropy's Gaussian2DKernel(kernel / 2),
+ * kernels = [1, size/32, size/8]), each divided by its largest magnitude over the whole bundle and
+ * weighted 0.2 / 0.3 / 0.5, the sum scaled per image to level * max(image) and added.
+ *
+ * The random fields are the reference's own draws, made by the host in the reference's order on
+ * the legacy stream (rsb_legacy_normal_fill) and uploaded as float32:
+ *  white_dev, field_a_dev, field_b_dev [n][size][size] float32: np.random.normal(size=shape) of
+ *               utils.py:291 and of the two noise_small calls (:277)
+ *  amp_a_dev, amp_b_dev [n] float32: max_noise = np.random.uniform(0, 1, n) of the two calls (:276)
+ *  level_dev    [n] float64: np.random.uniform(*noise_level, size=n) / 100   (:306-308)
+ *  image_dev, out_dev [n][size][size] float64 (out may be the image buffer itself)
+ *  size <= 1024 (the column pass keeps a 32-column tile with its halo in shared memory). */
+int rsb_noise_workspace_bytes(int n, int size, size_t* bytes);
+int rsb_add_noise(const double* image_dev, const float* white_dev, const float* field_a_dev,
+                  const float* field_b_dev, const float* amp_a_dev, const float* amp_b_dev,
+                  const double* level_dev, int n, int size, double* out_dev, void* workspace_dev,
+                  size_t workspace_bytes, void* stream);
+/* count draws of np.random.normal() (legacy stream, loc 0, scale 1) as float32, in stream order:
+ * the fields above (utils.py:277,291).  Host only; generator state as for rsb_jet_pack. */
+int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
+                           long long count, float* out);
+
 #ifdef __cplusplus
 }
 #endif

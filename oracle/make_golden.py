@@ -129,6 +129,22 @@ def mojave(ref):
     print("mojave ok", [d.shape for d in data])
 
 
+def noise(ref):
+    """add_noise (utils/utils.py:259-315) on small bundles: input images, result, RNG position."""
+    from radiosim.utils.utils import add_noise
+
+    for name, seed, n, size, level in [("noise_64", 11, 3, 64, [0, 15]), ("noise_100", 12, 2, 100, [5, 10])]:
+        rng = np.random.default_rng(seed)            # (input images only: any positive pattern will do)
+        yy, xx = np.mgrid[0:size, 0:size]
+        img = np.stack([np.exp(-((yy - rng.uniform(20, size - 20)) ** 2 + (xx - rng.uniform(20, size - 20)) ** 2)
+                               / (2 * rng.uniform(3, 9) ** 2)) * rng.uniform(0.01, 1.0) for _ in range(n)])[:, None]
+        np.random.seed(seed)
+        out = add_noise(img, level)
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), seed=seed, n=n, size=size, level=np.array(level),
+                            image=img, out=out, next_rand=np.random.rand())
+        print(name, "ok", out.shape, float(np.abs(out - img).max()))
+
+
 def main():
     sys.path.insert(0, ROOT)
     from oracle.refstub import load_reference
@@ -139,6 +155,7 @@ def main():
     surveys(ref)
     ppdisks(ref)
     mojave(ref)
+    noise(ref)
 
 
 if __name__ == "__main__":

@@ -386,3 +386,21 @@ extern "C" int rsb_survey_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_g
   *cached_gauss = g.gauss;
   return 0;
 }
+
+
+// `count` draws of RandomState.normal() (loc 0, scale 1: the value is legacy_gauss itself) as
+// float32 -- the noise fields of add_noise, reference src/radiosim/utils/utils.py:277,291
+// (np.random.normal(size=img_shape)), drawn in stream order.  Same state hand-over as rsb_jet_pack.
+extern "C" int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss,
+                                      double* cached_gauss, long long count, float* out) {
+  using namespace rsb::pack;
+  RSB_ARG(mt_key && mt_pos && has_gauss && cached_gauss && (out || count == 0),
+          "rsb_legacy_normal_fill: NULL argument");
+  RSB_ARG(count >= 0 && *mt_pos >= 0 && *mt_pos <= 624, "rsb_legacy_normal_fill: bad count / generator position");
+  Legacy g{mt_key, *mt_pos, *has_gauss, *cached_gauss};
+  for (long long i = 0; i < count; ++i) out[i] = (float)g.legacy_gauss();
+  *mt_pos = g.pos;
+  *has_gauss = g.has_gauss;
+  *cached_gauss = g.gauss;
+  return 0;
+}

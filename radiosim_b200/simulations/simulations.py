@@ -56,6 +56,23 @@ class _ShardWriter:
             self.pool.shutdown()
 
 
+def _noised_sky(sky, conf):
+    """jet / survey bundles with ``dataset.noise`` (``simulations.py:119-125``).  The reference's
+    condition ``noise_level > 0`` compares a list with an int and raises ``TypeError`` on its HEAD;
+    its intent -- add noise when a level above zero is configured, then bring every image back to
+    [0, 1] -- is what runs here."""
+    level = conf.dataset.noise_level
+    if not conf.dataset.noise or not max(level) > 0:
+        return sky
+    from ..utils import add_noise
+
+    out = add_noise(sky, level)
+    for img in out:
+        img -= img.min()
+        img /= img.max()
+    return out
+
+
 def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1):
     """One split: the bundles in ``bundles`` (an iterable of indices) -> one shard each."""
     from ..utils import create_grid
@@ -73,16 +90,20 @@ def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1)
                 from ..jets import create_jet
 
                 sky, target = create_jet(grid, conf)
-                writer.submit(path, {"x": sky, "y": target})
+                writer.submit(path, {"x": _noised_sky(sky, conf), "y": target})
             elif mode == "survey":
                 from ..survey import create_survey
 
                 sky, target = create_survey(grid, conf)
-                writer.submit(path, {"x": sky, "y": target})
+                writer.submit(path, {"x": _noised_sky(sky, conf), "y": target})
             elif mode == "mojave":
                 from ..mojave import create_mojave
 
                 data, names = create_mojave(conf, rng)
+                if conf.dataset.noise:  # simulations.py:101-108
+                    from ..utils import add_noise
+
+                    data[0] = add_noise(data[0][:, None], conf.dataset.noise_level)[:, 0]
                 writer.submit(path, dict(zip(names, data)))
             else:
                 raise ValueError(f"Mode {mode} not found. Choose 'survey', 'jet' or 'mojave' in config file")
@@ -97,12 +118,6 @@ def simulate_sky_distributions(conf, mode, rank=None, world=None):
     """``simulate_sky_distributions`` (``simulations.py:46-79``), sharded over ranks."""
     if rank is None or world is None:
         rank, world, _ = rank_info()
-    if getattr(conf.dataset, "noise", False):
-        # reference simulations.py:101-108,121-125 would call add_noise here; writing noise-free
-        # shards for a configuration that asks for noise would look valid and be wrong
-        raise NotImplementedError(
-            "dataset.noise = true: add_noise (reference utils/utils.py:259-315) is not available in "
-            "radiosim_b200 yet; set [dataset] noise = false (the reference's shipped rc file does)")
     seed = rank_seed(conf.general.seed, rank)
     if seed is not None:
         np.random.seed(seed)  # the legacy global stream, as tools/simulation_cli.py:38-40 does

@@ -135,3 +135,15 @@ def test_ellipse_mask_matches_torch_semantics():
         t2 = ((xx - 450) * np.sin(np.deg2rad(alpha)) - (yy - 450) * np.cos(np.deg2rad(alpha))) ** 2
         ref = ((t1 / a**2) + (t2 / b**2)) <= 1
         assert np.array_equal(ref.numpy(), opp.ellipse_mask(a, b, alpha))
+
+
+@pytest.mark.parametrize("name", ["noise_64", "noise_100"])
+def test_add_noise_oracle_matches_reference_golden(golden_dir, name):
+    """oracle.noise.add_noise against the unmodified reference's add_noise (utils/utils.py:259-315)."""
+    from oracle import noise as on
+
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    np.random.seed(int(g["seed"]))
+    out = on.add_noise(g["image"], list(g["level"]))
+    assert np.abs(out - g["out"]).max() <= 1e-12
+    assert np.random.rand() == float(g["next_rand"])
