@@ -275,7 +275,7 @@ def bench_survey(L, ev, hbm_peak, sfu_peak, prof, ns, n=4, size=1024):
     total = b.src_params.shape[0]
     bytes_img = 4 * size * size * 5
     rate = n / (ms * 1e-3)
-    p = prof.get("survey_tile", {})
+    p = prof.get("survey_tile", {}) if ns == 2000 else {}   # (the committed capture is the 2000-source case)
     out = {
         "config": f"C4: survey {size}x{size}, {ns} sources per image, class_distribution [2,1,2]",
         "images": n, "value": rate, "unit": UNIT, "ms_per_image": ms / n,
