@@ -212,6 +212,35 @@ int rsb_mojave_render(const void* recipes_dev, int n, const void* blobs_dev,
                       const float* profiles_dev, int size, unsigned flags, void* out_dev,
                       void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* The host half of create_mojave in C++ (reference src/radiosim/mojave/mojave.py:56-64: one child
+ * generator per image, rng.spawn; and the parameter draws of gen_compact :519-625, gen_one_jet
+ * :426-461, gen_two_jet :292-344, gen_shocks :182-199, add_swirl :250-254): numpy's SeedSequence
+ * spawning, PCG64 and the Generator distributions replayed bit for bit, scipy's expon / skewnorm
+ * draws by their construction.  Host only.
+ *   entropy [n_entropy], spawn_key [n_spawn_key] : the parent SeedSequence's entropy and spawn key
+ *     as 32-bit words (little-endian words of the integers); children first_child ..
+ *     first_child + n - 1 are the generators the reference's rng.spawn() calls would hand out
+ *   kinds [n] : 0 gen_compact, 1 gen_one_jet, 2 gen_two_jet
+ *   recipes [n] : 224-byte records as rsb_mojave_render takes them (blob0 = index into blob_params)
+ *   blob_params [blob_cap] : 64-byte records {double x, y, amp, width, length, a; int32 ref_r, ref_c,
+ *     pad[2]}: the skewed_gauss arguments of every blob; a shock carries in `amp` the factor drawn
+ *     at mojave.py:190 and in (ref_r, ref_c) the pixel of the jet so far it multiplies
+ *   *n_blobs_out : blobs written (an argument error if they exceed blob_cap) */
+int rsb_mojave_pack(const uint32_t* entropy, int n_entropy, const uint32_t* spawn_key, int n_spawn_key,
+                    long long first_child, int n, const int32_t* kinds, int size, void* recipes,
+                    void* blob_params, int blob_cap, int32_t* n_blobs_out);
+/* Device: blob_params -> the blob records and max-normalised 1-D profiles rsb_mojave_render reads
+ * (gauss.py:131-148; shock amplitudes resolved blob after blob, mojave.py:190).
+ *   blobs_out_dev [n_blobs] 16-byte records, profiles_out_dev [n_blobs][2][size] float32 */
+int rsb_mojave_blobs(const void* recipes_dev, int n, const void* blob_params_dev, int n_blobs, int size,
+                     void* blobs_out_dev, float* profiles_out_dev, void* stream);
+/* For tests: PCG64 (state, inc) of spawned children as numpy reports them, and raw draws of one
+ * Generator method from such a state (kind 0 random, 1 standard_normal, 2 standard_exponential,
+ * 3 power(a), 4 integers(a, b), 5 uniform(a, b)); state4 = {state hi, state lo, inc hi, inc lo}. */
+int rsb_pcg64_spawn_states(const uint32_t* entropy, int n_entropy, const uint32_t* spawn_key, int n_spawn_key,
+                           long long first_child, int n, uint64_t* out);
+int rsb_pcg64_draws(uint64_t* state4, int kind, double a, double b, int count, double* out);
+
 /* ---------------------------------------------------------------- utilities */
 /* idx of zoom_on_source (src/radiosim/utils/utils.py:111-119): smallest distance from any
  * pixel > threshold to the border of a size x size float64 image; `size` if there is none

@@ -115,6 +115,81 @@ __global__ void __launch_bounds__(256) pre_kernel(const Recipe* __restrict__ rec
   }
 }
 
+// ---- blobs as drawn -> max-normalised 1-D profiles + amplitudes ---------------------------
+// skewed_gauss (gauss.py:131-148): normal = norm.pdf(rows; y, width) / max, skew =
+// skewnorm.pdf(cols; a, x, length) / max, maxima over the INTEGER samples.  A shock's amplitude is
+// the value of the jet built so far at one pixel times a drawn factor (mojave.py:190), so the blobs
+// of a jet are finished one after the other.  Float64 throughout; one CTA per jet.
+struct BlobParam {  // = rsb::mjpack::BlobParam (csrc/mojave_pack.cu)
+  double x, y, amp, width, length, a;
+  int ref_r, ref_c;
+  int pad[2];
+};
+constexpr int kMaxJetBlobs = 32;
+
+__device__ __forceinline__ double normal_pdf_at(const BlobParam& p, int i) {
+  const double t = ((double)i - p.y) / p.width;
+  return exp(-(t * t) / 2.0) / 2.5066282746310002 / p.width;   // sqrt(2 pi)
+}
+__device__ __forceinline__ double skew_pdf_at(const BlobParam& p, int i) {
+  const double u = ((double)i - p.x) / p.length;
+  // 2 phi(u) Phi(a u) / length, Phi(z) = erfc(-z / sqrt 2) / 2
+  return 2.0 * (exp(-(u * u) / 2.0) / 2.5066282746310002) * (0.5 * erfc(-(p.a * u) * 0.7071067811865476)) / p.length;
+}
+
+__global__ void __launch_bounds__(256) blob_kernel(const Recipe* __restrict__ recipes,
+                                                   const BlobParam* __restrict__ bp, int N,
+                                                   Blob* __restrict__ blobs, float* __restrict__ prof) {
+  const Recipe& R = recipes[blockIdx.x >> 1];
+  const int j = blockIdx.x & 1, b0 = R.blob0[j], nb = min(R.nblob[j], kMaxJetBlobs);
+  if (nb <= 0) return;
+  __shared__ double s_nmax[kMaxJetBlobs], s_smax[kMaxJetBlobs], s_amp[kMaxJetBlobs];
+  __shared__ double s_red[2][8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int k = 0; k < nb; ++k) {
+    const BlobParam p = bp[b0 + k];
+    double nm = 0.0, sm = 0.0;   // pdf values are >= 0
+    for (int i = tid; i < N; i += blockDim.x) {
+      nm = fmax(nm, normal_pdf_at(p, i));
+      sm = fmax(sm, skew_pdf_at(p, i));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      nm = fmax(nm, __shfl_xor_sync(0xffffffffu, nm, o));
+      sm = fmax(sm, __shfl_xor_sync(0xffffffffu, sm, o));
+    }
+    if (lane == 0) { s_red[0][warp] = nm; s_red[1][warp] = sm; }
+    __syncthreads();
+    if (tid == 0) {
+      double a = 0.0, b = 0.0;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { a = fmax(a, s_red[0][w]); b = fmax(b, s_red[1][w]); }
+      s_nmax[k] = a;
+      s_smax[k] = b;
+      double amp = p.amp;
+      if (p.ref_r >= 0) {  // jet.pixel(r, c) of the blobs before this one, summed in build order
+        double sum = 0.0;
+        for (int q = 0; q < k; ++q) {
+          const BlobParam pq = bp[b0 + q];
+          const double v = ((normal_pdf_at(pq, p.ref_r) / s_nmax[q]) * (skew_pdf_at(pq, p.ref_c) / s_smax[q])) * s_amp[q];
+          sum = sum + (fabs(v) <= 1e-8 ? 0.0 : v);
+        }
+        amp = sum * p.amp;
+      }
+      s_amp[k] = amp;
+      Blob out;
+      out.amp = (float)amp; out.pad = 0; out.prof = (long long)(b0 + k) * 2 * N;
+      blobs[b0 + k] = out;
+    }
+    __syncthreads();
+    const double inm = s_nmax[k], ism = s_smax[k];
+    float* dst = prof + (size_t)(b0 + k) * 2 * N;
+    for (int i = tid; i < N; i += blockDim.x) {
+      dst[i] = (float)(normal_pdf_at(p, i) / inm);
+      dst[N + i] = (float)(skew_pdf_at(p, i) / ism);
+    }
+  }
+}
+
 template <typename OutT>
 __global__ void __launch_bounds__(256) rot_kernel(const Recipe* __restrict__ recipes,
                                                   const float* __restrict__ G, int N,
@@ -193,6 +268,17 @@ int rsb_mojave_workspace_bytes(int n, int size, size_t* bytes) {
   RSB_ARG(bytes && n >= 0 && size >= 2, "rsb_mojave_workspace_bytes: bad arguments");
   const size_t px = (size_t)size * size;
   *bytes = 2 * (size_t)n * px * sizeof(float) + (((size_t)n * 8 + 255) & ~(size_t)255) + 256;
+  return 0;
+}
+
+int rsb_mojave_blobs(const void* recipes, int n, const void* blob_params, int n_blobs, int size,
+                     void* blobs_out, float* profiles_out, void* stream) {
+  RSB_ARG(n >= 0 && n_blobs >= 0 && size >= 2, "rsb_mojave_blobs: bad n / n_blobs / size (%d, %d, %d)", n, n_blobs, size);
+  if (n == 0 || n_blobs == 0) return 0;
+  RSB_ARG(recipes && blob_params && blobs_out && profiles_out, "rsb_mojave_blobs: NULL buffer");
+  blob_kernel<<<2 * n, 256, 0, (cudaStream_t)stream>>>((const Recipe*)recipes, (const BlobParam*)blob_params, size,
+                                                     (Blob*)blobs_out, profiles_out);
+  RSB_LAUNCHED();
   return 0;
 }
 

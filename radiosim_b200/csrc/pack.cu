@@ -120,11 +120,19 @@ inline double slot_at(const SlotRot& s, double r, double c) {
 // counts[0..2]: images decided by (1), by (2), by the full evaluation.
 inline bool border_below(const SlotRot* s, int slots, int size, long long* counts) {
   const double thr = 0.01, last = (double)(size - 1);
-  double upper = 0.0, best = -1.0;
+  // Per border line (r = 0, r = N-1, c = 0, c = N-1) and slot: the slot's largest value on the whole
+  // line, where along the line it sits and how fast it falls off there:
+  //   value(t) = amp * exp(-(qmin + curv * (t - t0)^2) / 2),  t = the pixel's coordinate along the line
+  struct LineSlot { double vmax, t0, curv; };
+  LineSlot ls[4][2 * kMaxHi];
+  double upper[4] = {0.0, 0.0, 0.0, 0.0}, best = -1.0;
   double best_r = 0.0, best_c = 0.0;
-  bool bounded = true;
-  for (int k = 0; k < slots; ++k) {
-    if (s[k].amp == 0.0) continue;
+  bool bounded = slots <= 2 * kMaxHi;
+  for (int k = 0; k < slots && bounded; ++k) {
+    if (s[k].amp == 0.0) {
+      for (int l = 0; l < 4; ++l) ls[l][k] = LineSlot{0.0, 0.0, 0.0};
+      continue;
+    }
     const double iy = 1.0 / (s[k].wy * s[k].wy), ix = 1.0 / (s[k].wx * s[k].wx);
     const double mrr = s[k].cs * s[k].cs * iy + s[k].sn * s[k].sn * ix;
     const double mcc = s[k].sn * s[k].sn * iy + s[k].cs * s[k].cs * ix;
@@ -132,27 +140,35 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
     const double det = mrr * mcc - mrc * mrc;
     // centre in (row, column): ra = cy cs - cx sn, rb = cy sn + cx cs  ->  cy, cx
     const double cy = s[k].ra * s[k].cs + s[k].rb * s[k].sn, cx = s[k].rb * s[k].cs - s[k].ra * s[k].sn;
-    if (!(det > 0.0) || !std::isfinite(det) || !std::isfinite(cy) || !std::isfinite(cx)) {
+    if (!(det > 0.0) || !std::isfinite(det) || !std::isfinite(cy) || !std::isfinite(cx) || !(mrr > 0.0) ||
+        !(mcc > 0.0)) {
       bounded = false;
       break;
     }
-    double qmin = INFINITY, pr = 0.0, pc = 0.0;
     const double rows[2] = {0.0, last};
-    for (int e = 0; e < 2; ++e) {  // lines r = 0, r = N-1: minimum over the column offset
+    for (int e = 0; e < 2; ++e) {  // lines r = 0, r = N-1: along the line the column varies
       const double dr = rows[e] - cy, q = dr * dr * det / mcc;
-      if (q < qmin) { qmin = q; pr = rows[e]; pc = cx - mrc * dr / mcc; }
+      const double v = std::fabs(s[k].amp) * std::exp(-0.5 * q * 0.999999);
+      const double t0 = cx - mrc * dr / mcc;
+      ls[e][k] = LineSlot{v, t0, mcc * 0.999999};
+      upper[e] += v;
+      if (v > best) { best = v; best_r = rows[e]; best_c = t0; }
     }
-    for (int e = 0; e < 2; ++e) {  // lines c = 0, c = N-1
+    for (int e = 0; e < 2; ++e) {  // lines c = 0, c = N-1: the row varies
       const double dc = rows[e] - cx, q = dc * dc * det / mrr;
-      if (q < qmin) { qmin = q; pc = rows[e]; pr = cy - mrc * dc / mrr; }
+      const double v = std::fabs(s[k].amp) * std::exp(-0.5 * q * 0.999999);
+      const double t0 = cy - mrc * dc / mrr;
+      ls[2 + e][k] = LineSlot{v, t0, mrr * 0.999999};
+      upper[2 + e] += v;
+      if (v > best) { best = v; best_r = t0; best_c = rows[e]; }
     }
-    const double v = std::fabs(s[k].amp) * std::exp(-0.5 * qmin * 0.999999);
-    upper += v;
-    if (v > best) { best = v; best_r = pr; best_c = pc; }
   }
-  if (bounded && upper * 1.000001 < 0.0099) {
-    counts[0]++;
-    return true;
+  if (bounded) {
+    const double u = std::fmax(std::fmax(upper[0], upper[1]), std::fmax(upper[2], upper[3]));
+    if (u * 1.000001 < 0.0099) {  // (1): no border pixel can reach the threshold
+      counts[0]++;
+      return true;
+    }
   }
   auto pixel = [&](double r, double c) {
     double sum = 0.0;
@@ -162,13 +178,51 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
   if (bounded && best >= 0.0) {
     const double r = std::fmin(std::fmax(std::nearbyint(best_r), 0.0), last);
     const double c = std::fmin(std::fmax(std::nearbyint(best_c), 0.0), last);
-    if (!(pixel(r, c) < thr)) {  // (a NaN sum makes the reference's `max < 0.01` false as well)
+    if (!(pixel(r, c) < thr)) {  // (2) (a NaN sum makes the reference's `max < 0.01` false as well)
       counts[1]++;
       return false;
     }
   }
   counts[2]++;
-  // np.max propagates NaN, and `nan < 0.01` is False
+  if (bounded) {
+    // (3a) the full evaluation without the terms that cannot matter: on every line a slot only counts
+    // where its own value can exceed `tiny`; what is left out is below slots * tiny per pixel.  The
+    // verdict is taken from these sums unless the maximum lands within that margin of the threshold.
+    const double tiny = 1e-14, margin = 2.0 * kMaxHi * tiny + 1e-15;
+    bool all_amp_nonneg = true;
+    for (int k = 0; k < slots; ++k) all_amp_nonneg = all_amp_nonneg && !(s[k].amp < 0.0);
+    if (all_amp_nonneg) {
+      double m = 0.0;
+      bool above = false;
+      for (int l = 0; l < 4 && !above; ++l) {
+        int lo[2 * kMaxHi], hi[2 * kMaxHi], first = size, end = -1;
+        for (int k = 0; k < slots; ++k) {
+          lo[k] = 1; hi[k] = 0;
+          const LineSlot& q = ls[l][k];
+          if (!(q.vmax > tiny)) continue;
+          // vmax * exp(-curv (t - t0)^2 / 2) > tiny  <=>  |t - t0| < sqrt(2 ln(vmax / tiny) / curv)
+          const double reach = std::sqrt(2.0 * std::log(q.vmax / tiny) / q.curv) + 1.0;
+          const double a0 = std::fmax(std::floor(q.t0 - reach), 0.0), a1 = std::fmin(std::ceil(q.t0 + reach), last);
+          if (!(a0 <= a1)) continue;
+          lo[k] = (int)a0; hi[k] = (int)a1;
+          if (lo[k] < first) first = lo[k];
+          if (hi[k] > end) end = hi[k];
+        }
+        const double fixed = (l & 1) ? last : 0.0;
+        for (int i = first; i <= end; ++i) {
+          double sum = 0.0;
+          const double t = (double)i;
+          for (int k = 0; k < slots; ++k)
+            if (lo[k] <= i && i <= hi[k]) sum += (l < 2) ? slot_at(s[k], fixed, t) : slot_at(s[k], t, fixed);
+          if (sum > m) m = sum;
+          if (sum >= thr + margin) { above = true; break; }
+        }
+      }
+      if (above || m >= thr + margin) return false;
+      if (m + margin < thr) return true;
+    }
+  }
+  // (3b) the reference's evaluation, term for term (np.max propagates NaN, and `nan < 0.01` is False)
   double m = -INFINITY;
   bool nan = false;
   for (int i = 0; i < size; ++i) {

@@ -12,6 +12,7 @@ a shock's amplitude is read from (``mojave.py:190``), from the 1-D profiles.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 from scipy.special import ndtr
@@ -27,7 +28,9 @@ RECIPE = np.dtype([("g", GAUSS, (3,)), ("strength", "<f8", (2,)), ("radius", "<f
                    ("angle", "<f8"), ("amp", "<f8"), ("blob0", "<i4", (2,)), ("nblob", "<i4", (2,)),
                    ("flip1", "<i4"), ("compact", "<i4"), ("pad", "<i4", (2,))])
 BLOB = np.dtype([("amp", "<f4"), ("pad", "<i4"), ("prof", "<i8")])
-assert RECIPE.itemsize == 224 and BLOB.itemsize == 16
+BLOBP = np.dtype([("x", "<f8"), ("y", "<f8"), ("amp", "<f8"), ("width", "<f8"), ("length", "<f8"), ("a", "<f8"),
+                  ("ref_r", "<i4"), ("ref_c", "<i4"), ("pad", "<i4", (2,))])
+assert RECIPE.itemsize == 224 and BLOB.itemsize == 16 and BLOBP.itemsize == 64
 
 
 def _as_rng(rng):
@@ -54,9 +57,11 @@ def _skewnorm_rvs(rng, a, loc, scale):
 class _Blob:
     """amp * normal[row] * skew[col] (``src/radiosim/utils/gauss.py:131-148``)."""
 
-    __slots__ = ("amp", "normal", "skew")
+    __slots__ = ("amp", "normal", "skew", "args", "factor", "ref")
 
     def __init__(self, size, x, y, amp, width, length, a):
+        self.args = (x, y, amp, width, length, a)   # as drawn (compared with the native packer)
+        self.factor, self.ref = None, None          # shocks: amplitude = jet pixel `ref` x `factor`
         vals = np.arange(size)
         t = (vals - y) / width
         normal = np.exp(-(t**2) / 2.0) / np.sqrt(2 * np.pi) / width
@@ -104,11 +109,13 @@ def _add_shocks(jet, n_shock, length, width, sx, rng):
         r, c = int(py), int(px)
         if not (-size <= r < size and -size <= c < size):   # the reference's IndexError
             continue
-        s_amp = jet.pixel(r % size, c % size) * rng.uniform(0.03, 0.6)
+        factor = rng.uniform(0.03, 0.6)
+        s_amp = jet.pixel(r % size, c % size) * factor
         s_sx = rng.uniform(*np.sort([2, width]))
         s_sy = rng.uniform(*np.sort([s_sx, length / n_shock]))
         s_a = rng.uniform(5, 9)
         jet.blobs.append(_Blob(size, int(px), int(py), s_amp, s_sx, s_sy, s_a))
+        jet.blobs[-1].factor, jet.blobs[-1].ref = factor, (r % size, c % size)
         dist += step
 
 
@@ -324,6 +331,82 @@ def render_packed(rec, blob_arr, prof_arr, size, f64=True, chunk=2048):
     return out
 
 
+def _words(v: int) -> np.ndarray:
+    out = []
+    while True:
+        out.append(v & 0xFFFFFFFF)
+        v >>= 32
+        if v == 0:
+            return np.array(out, dtype=np.uint32)
+
+
+def native_recipes(rng, amount, size):
+    """The host half of ``create_mojave`` (``mojave.py:56-64`` + the ``gen_*`` draws) natively
+    (``rsb_mojave_pack``): the children the three ``rng.spawn`` calls would hand out are derived from
+    the parent's seed sequence in C++, their draws replayed, and the parent's spawn counter moved on
+    as ``spawn`` would.  Returns ``(recipes, blob parameters)`` or ``None`` when the parent is not a
+    PCG64 generator on a plain integer-seeded ``SeedSequence`` (then the Python packer runs)."""
+    bg = rng.bit_generator
+    ss = getattr(bg, "seed_seq", None)
+    if (type(bg).__name__ != "PCG64" or type(ss) is not np.random.SeedSequence or ss.pool_size != 4
+            or not isinstance(ss.entropy, (int, np.integer)) or ss.entropy < 0
+            or not all(isinstance(k, (int, np.integer)) and 0 <= k for k in ss.spawn_key)):
+        return None
+    n = int(np.sum(amount))
+    first = ss.n_children_spawned
+    if first + n >= 2**32 or len(ss.spawn_key) > 8:
+        return None
+    entropy = _words(int(ss.entropy))
+    key = (np.concatenate([_words(int(k)) for k in ss.spawn_key]) if ss.spawn_key else np.zeros(0, np.uint32))
+    kinds = np.repeat(np.arange(3, dtype=np.int32), np.asarray(amount, dtype=np.int64))
+    rec = np.zeros(n, dtype=RECIPE)
+    cap = 24 * max(n, 1)          # <= 2 jets x (1 + 10 shocks) per image
+    bp = np.zeros(cap, dtype=BLOBP)
+    nb = C.c_int32(0)
+    L.check(L.lib().rsb_mojave_pack(entropy.ctypes.data, len(entropy), key.ctypes.data if len(key) else None,
+                                    len(key), first, n, kinds.ctypes.data, size, rec.ctypes.data, bp.ctypes.data,
+                                    cap, C.byref(nb)), "rsb_mojave_pack")
+    # the three spawn() calls of the reference leave the parent's child counter n further on
+    moved = np.random.SeedSequence(ss.entropy, spawn_key=ss.spawn_key, pool_size=ss.pool_size,
+                                   n_children_spawned=first + n)
+    bg.__setstate__((bg.state, moved))
+    return rec, bp[: nb.value]
+
+
+def render_native(rec, bp, size, f64=True, chunk=2048):
+    """Recipes + blob parameters (:func:`native_recipes`) -> images; profiles and shock amplitudes are
+    finished on the device (``rsb_mojave_blobs``)."""
+    L.require_device()
+    lib = L.lib()
+    n = len(rec)
+    dt = np.float64 if f64 else np.float32
+    out = L.pinned_empty((n, size, size), dt)
+    nb = max(len(bp), 1)
+    d_bp = L.dev_from(bp if len(bp) else np.zeros(1, dtype=BLOBP))
+    d_blobs, d_prof = L.DeviceBuffer(nb * 16), L.DeviceBuffer(nb * 2 * size * 4)
+    max_imgs = max(1, min(chunk, (1 << 30) // (size * size * 8)))
+    keep = []
+    for i0 in range(0, n, max_imgs):
+        cnt = min(max_imgs, n - i0)
+        need = C.c_size_t(0)
+        L.check(lib.rsb_mojave_workspace_bytes(cnt, size, C.byref(need)))
+        d_r, (p_r,), stage = L.upload_blob([rec[i0 : i0 + cnt]])
+        d_w = L.DeviceBuffer(need.value)
+        d_o = L.DeviceBuffer(cnt * size * size * np.dtype(dt).itemsize)
+        L.check(lib.rsb_mojave_blobs(p_r, cnt, d_bp.ptr, len(bp), size, d_blobs.ptr, d_prof.ptr, None),
+                "rsb_mojave_blobs")
+        L.check(lib.rsb_mojave_render(p_r, cnt, d_blobs.ptr, d_prof.ptr, size, L.JET_OUT_F64 if f64 else 0,
+                                      d_o.ptr, d_w.ptr, d_w.nbytes, None), "rsb_mojave_render")
+        dst = out[i0 : i0 + cnt]
+        L.check(lib.rsb_memcpy_d2h(dst.ctypes.data, d_o.ptr, dst.nbytes, None), "d2h")
+        keep.append((d_r, stage, d_w, d_o))
+        if len(keep) > 2:
+            L.device_sync()
+            keep.clear()
+    L.device_sync()
+    return out
+
+
 def render_sources(sources, size, f64=True, chunk=2048):
     """Evaluate recipes on the device -> ``[n, size, size]`` float64 (or float32)."""
     return render_packed(*pack_recipes(sources, size), size, f64=f64, chunk=chunk)
@@ -411,12 +494,17 @@ def create_mojave(conf, rng, today=None):
     size = conf.dataset.img_size
     bundle_size = conf.dataset.bundle_size
     amount = class_counts(conf.mojave.class_ratio, bundle_size)
-    rec, blob_arr, prof_arr = make_recipes(rng, amount, size, threads)
+    native = None if os.environ.get("RSB_PY_PACKER") == "1" else native_recipes(rng, amount, size)
+    if native is None:
+        rec, blob_arr, prof_arr = make_recipes(rng, amount, size, threads)
     classes = np.repeat(np.arange(3), amount)
     order = np.arange(bundle_size)
     rng.shuffle(order)
     # rendered in shuffled order, so the images need no host-side permutation afterwards
-    jets_shuffled = render_packed(rec[order], blob_arr, prof_arr, size)
+    if native is not None:
+        jets_shuffled = render_native(native[0][order], native[1], size)
+    else:
+        jets_shuffled = render_packed(rec[order], blob_arr, prof_arr, size)
     ra = rng.uniform(0, 360, size=bundle_size)      # utils.py:386-390
     dec = rng.uniform(-30, 87, size=bundle_size)
     start = np.datetime64("1995-01-01")             # utils.py:393-406

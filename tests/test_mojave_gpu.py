@@ -115,3 +115,23 @@ def test_kernel_swirl_identity_and_direction():
     expect = -s * np.exp(-rho / (radius / 5 * np.log(2)))
     assert ang(plain) == pytest.approx(0.0, abs=2e-2)
     assert ang(sw) < -0.05 and ang(sw) == pytest.approx(expect, abs=0.08)   # (a flux-weighted mean over rho)
+
+
+def test_native_recipes_render_like_the_python_packer():
+    """create_mojave through the native recipe generator (rsb_mojave_pack + rsb_mojave_blobs: profiles and
+    shock amplitudes finished on the device) against the Python packer path on the same generator."""
+    from radiosim_b200.mojave import create_mojave
+
+    conf = SimpleNamespace(general=SimpleNamespace(threads=None),
+                           dataset=SimpleNamespace(img_size=128, bundle_size=90),
+                           mojave=SimpleNamespace(class_ratio=[1, 1, 1]))
+    today = datetime.date(2026, 1, 1)
+    a, names = create_mojave(conf, np.random.default_rng(77), today=today)
+    os.environ["RSB_PY_PACKER"] = "1"
+    try:
+        b, _ = create_mojave(conf, np.random.default_rng(77), today=today)
+    finally:
+        del os.environ["RSB_PY_PACKER"]
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+    for i in range(90):
+        assert np.abs(a[0][i] - b[0][i]).max() <= TOL * b[0][i].max(), i
