@@ -53,6 +53,7 @@ int rsb_device_sync(void);
 int rsb_event_create(void** event);
 int rsb_event_destroy(void* event);
 int rsb_event_record(void* event, void* stream);
+int rsb_stream_wait_event(void* stream, void* event); /* later work of `stream` waits for `event` */
 int rsb_event_elapsed_ms(void* start, void* stop, float* ms); /* syncs on stop */
 /* kernels launched by this library since load (all devices, this process) */
 int rsb_launch_count(uint64_t* count);

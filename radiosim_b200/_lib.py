@@ -55,6 +55,7 @@ _SIGS = {
     "rsb_event_create": ([C.POINTER(_vp)], _i32),
     "rsb_event_destroy": ([_vp], _i32),
     "rsb_event_record": ([_vp, _vp], _i32),
+    "rsb_stream_wait_event": ([_vp, _vp], _i32),
     "rsb_event_elapsed_ms": ([_vp, _vp, C.POINTER(C.c_float)], _i32),
     "rsb_launch_count": ([C.POINTER(C.c_uint64)], _i32),
     "rsb_bench_sfu": ([_i32, C.POINTER(C.c_double)], _i32),
@@ -274,6 +275,37 @@ def pinned_empty(shape, dtype) -> np.ndarray:
     buf = (C.c_char * max(nbytes, 1)).from_address(owner.ptr)
     buf._rsb_owner = owner
     return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+
+class CopyStream:
+    """A second stream for device-to-host copies that overlap the default stream's kernels:
+    ``after_default()`` makes its next operations wait for everything enqueued on the default stream
+    so far."""
+
+    _cache: dict = {}
+
+    @classmethod
+    def get(cls):
+        dev = _CUR_DEV[0]
+        if dev not in cls._cache:
+            cls._cache[dev] = cls()
+        return cls._cache[dev]
+
+    def __init__(self):
+        s, e = _vp(), _vp()
+        check(_lib.rsb_stream_create(C.byref(s)), "rsb_stream_create")
+        check(_lib.rsb_event_create(C.byref(e)), "rsb_event_create")
+        self.stream, self.event = s, e
+
+    def after_default(self):
+        check(_lib.rsb_event_record(self.event, None), "rsb_event_record")
+        check(_lib.rsb_stream_wait_event(self.stream, self.event), "rsb_stream_wait_event")
+
+    def d2h(self, dst: np.ndarray, dev_ptr: int):
+        check(_lib.rsb_memcpy_d2h(dst.ctypes.data, dev_ptr, dst.nbytes, self.stream), "d2h")
+
+    def sync(self):
+        check(_lib.rsb_stream_sync(self.stream), "rsb_stream_sync")
 
 
 def upload_blob(arrays):

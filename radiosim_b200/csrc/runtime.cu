@@ -131,6 +131,10 @@ int rsb_event_record(void* event, void* stream) {
   RSB_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
   return 0;
 }
+int rsb_stream_wait_event(void* stream, void* event) {
+  RSB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0));
+  return 0;
+}
 int rsb_event_elapsed_ms(void* start, void* stop, float* ms) {
   RSB_ARG(ms != nullptr, "rsb_event_elapsed_ms: NULL out pointer");
   RSB_CUDA(cudaEventSynchronize((cudaEvent_t)stop));

@@ -384,7 +384,10 @@ def render_native(rec, bp, size, f64=True, chunk=2048):
     nb = max(len(bp), 1)
     d_bp = L.dev_from(bp if len(bp) else np.zeros(1, dtype=BLOBP))
     d_blobs, d_prof = L.DeviceBuffer(nb * 16), L.DeviceBuffer(nb * 2 * size * 4)
-    max_imgs = max(1, min(chunk, (1 << 30) // (size * size * 8)))
+    # chunks of ~64 MB of results: a chunk's copy to the host (second stream) runs under the next
+    # chunk's kernels (default stream)
+    max_imgs = max(1, min(chunk, (64 << 20) // (size * size * np.dtype(dt).itemsize)))
+    copier = L.CopyStream.get()
     keep = []
     for i0 in range(0, n, max_imgs):
         cnt = min(max_imgs, n - i0)
@@ -397,12 +400,13 @@ def render_native(rec, bp, size, f64=True, chunk=2048):
                 "rsb_mojave_blobs")
         L.check(lib.rsb_mojave_render(p_r, cnt, d_blobs.ptr, d_prof.ptr, size, L.JET_OUT_F64 if f64 else 0,
                                       d_o.ptr, d_w.ptr, d_w.nbytes, None), "rsb_mojave_render")
-        dst = out[i0 : i0 + cnt]
-        L.check(lib.rsb_memcpy_d2h(dst.ctypes.data, d_o.ptr, dst.nbytes, None), "d2h")
+        copier.after_default()
+        copier.d2h(out[i0 : i0 + cnt], d_o.ptr)
         keep.append((d_r, stage, d_w, d_o))
-        if len(keep) > 2:
-            L.device_sync()
-            keep.clear()
+        if len(keep) > 3:               # bound the blocks held by chunks still being copied
+            copier.sync()
+            del keep[:-1]
+    copier.sync()
     L.device_sync()
     return out
 
