@@ -343,6 +343,87 @@ def bench_mojave(L, ev, hbm_peak, n=10_000, size=256):
     }
 
 
+def bench_c1(L, ev, hbm_peak, sfu_peak):
+    """C1: rc/default_simulation.toml as shipped (jets 128^2, 40 bundles of 20, list targets): device rate of the
+    kernel on the same 800 images, and the whole `simulate` path (RNG chain, render, .h5 shards on disk)."""
+    import shutil
+    import tempfile
+
+    from radiosim_b200.io import Config
+    from radiosim_b200.jets.packer import pack_jets
+    from radiosim_b200.simulations import simulate_sky_distributions
+
+    lib = L.lib()
+    n, size = 800, 128
+    np.random.seed(1337)
+    jb = pack_jets(n, size, COMPS, "normalize")
+    d_p, d_z = L.dev_from(jb.params), L.dev_from(jb.zoom_pad)
+    d_img, d_m, d_k = L.DeviceBuffer(n * size * size * 4), L.DeviceBuffer(n * 4), L.DeviceBuffer(n * 8)
+
+    def enqueue():
+        L.check(lib.rsb_jet_render(d_p.ptr, d_z.ptr, n, SLOTS, size, L.JET_NORMALIZE, d_img.ptr, d_m.ptr, d_k.ptr,
+                                   None, 0, None))
+
+    ms = ev.time(enqueue, reps=20, warm=3)
+    conf = Config.from_toml(os.path.join(ROOT, "rc", "default_simulation.toml"))
+    walls, nbytes = [], 0
+    for rep in range(3):
+        tmp = tempfile.mkdtemp(prefix="rsb_c1_")
+        try:
+            conf.paths.outpath = tmp
+            t = time.perf_counter()
+            files = simulate_sky_distributions(conf, "jet", rank=0, world=1)
+            walls.append(time.perf_counter() - t)
+            nbytes = sum(os.path.getsize(f) for f in files)
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+    live = float((jb.params[:, :, 0] != 0).sum()) / n
+    rate = n / (ms * 1e-3)
+    bytes_img = 4 * size * size + SLOTS * 48 + 16
+    return {
+        "config": "C1: jet simulation from rc/default_simulation.toml, 128x128, 40 bundles of 20 images, list targets",
+        "images": n, "value": rate, "unit": UNIT, "ms_per_image": ms / n,
+        "e2e": {"value": n / min(walls), "unit": UNIT, "shard_bytes": nbytes,
+                "call": "simulate_sky_distributions(conf, 'jet'): RNG chain, render, float64 results, 40 .h5 shards "
+                        "written to local disk (best of 3)"},
+        "roofline": {"bound": "hbm", "achieved": rate * bytes_img / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": rate * bytes_img / 1e9 / hbm_peak, "algorithmic_bytes_per_image": bytes_img,
+                     "traffic": None, "governing": "sfu", "algorithmic_ex2_per_image": size * size * live,
+                     "sfu_frac": rate * size * size * live / sfu_peak,
+                     "note": "800 images are 5.4 per SM: a launch this small is mostly ramp-up and tail"},
+    }
+
+
+def bench_pipeline(L, n_bundles=8, bundle=500, size=256):
+    """the whole `simulate --mode jet` path at 256^2 (RNG chain, render, float64 results to the
+    host, .h5 shards written by background threads)."""
+    import shutil
+    import tempfile
+
+    from radiosim_b200.io import Config
+    from radiosim_b200.simulations import simulate_sky_distributions
+
+    conf = Config.from_toml(os.path.join(ROOT, "rc", "default_simulation.toml"))
+    conf.dataset.img_size, conf.dataset.bundle_size = size, bundle
+    conf.dataset.bundles_train, conf.dataset.bundles_valid, conf.dataset.bundles_test = n_bundles, 0, 0
+    best, nbytes = None, 0
+    for rep in range(2):
+        tmp = tempfile.mkdtemp(prefix="rsb_pipe_")
+        try:
+            conf.paths.outpath = tmp
+            t = time.perf_counter()
+            files = simulate_sky_distributions(conf, "jet", rank=0, world=1)
+            dt = time.perf_counter() - t
+            nbytes = sum(os.path.getsize(f) for f in files)
+            best = dt if best is None else min(best, dt)
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+    n = n_bundles * bundle
+    return {"config": f"simulate --mode jet, {size}x{size}, {n_bundles} bundles of {bundle} (float64 .h5 shards)",
+            "images": n, "value": n / best, "unit": UNIT, "written_gb_per_s": nbytes / best / 1e9,
+            "shard_bytes": nbytes, "note": "end to end incl. the files (page cache of the box's local disk)"}
+
+
 def bench_ppdisk(L, ev, hbm_peak, n=50, size=512):
     """C3: ppdisk 512^2 with the ranges of rc/default_ppdisks_simulation.toml (batch_size 5 x 10)."""
     from radiosim_b200.ppdisks import ppdisks as pp
@@ -579,11 +660,15 @@ def run_cuda(args):
         if world == 1 and not args.no_configs:
             evs = _Events(L)
             cfgs = []
-            for fn, kw in ((bench_mojave, {}), (bench_ppdisk, {}),
-                           (bench_survey, {"ns": 2000}), (bench_survey, {"ns": 5000})):
+            for fn, kw in ((bench_c1, {}), (bench_mojave, {}), (bench_ppdisk, {}),
+                           (bench_survey, {"ns": 2000}), (bench_survey, {"ns": 5000}), (bench_pipeline, {})):
                 try:
                     if fn is bench_survey:
                         cfgs.append(fn(L, evs, hbm_peak, sfu.value, prof, **kw))
+                    elif fn is bench_c1:
+                        cfgs.append(fn(L, evs, hbm_peak, sfu.value))
+                    elif fn is bench_pipeline:
+                        cfgs.append(fn(L))
                     else:
                         cfgs.append(fn(L, evs, hbm_peak, **kw))
                 except Exception as exc:  # a broken side config must not lose the headline line

@@ -265,6 +265,8 @@ int rsb_resize_linear(const double* src_dev, int src_size, int src_pitch, size_t
  * for images too large for shared memory the per-CTA raw-image slots come from a 32 MiB
  * array compiled into the library.  That array occupies 32 MiB on every GPU that loads
  * librsb200.so, until the process exits.
+ *  - sizes the on-chip renderer takes (up to 256) need no scratch: they run exactly as under
+ *    rsb_jet_render and leave the array untouched.
  *  - limit: size <= 512 (larger sizes return an argument error; use rsb_jet_render).
  *    At 256x256 the array holds 128 slots, at 512x512 32, so fewer CTAs are resident
  *    than with a caller workspace; the images are identical.

@@ -624,7 +624,7 @@ struct HostCtx {
   void* work[kLanes] = {nullptr, nullptr, nullptr};
   size_t cap_params = 0, cap_out = 0, cap_n = 0, cap_work = 0;
 };
-std::mutex g_host_mu;
+std::mutex g_host_mu[64];  // one per device: host threads driving different GPUs do not wait on each other
 HostCtx g_host_ctx[64];
 
 int grow(void** p, size_t bytes) {
@@ -643,7 +643,7 @@ int rsb_jet_render_host(const double* params, const int32_t* zoom_pad, int n, in
   int dev = 0;
   RSB_CUDA(cudaGetDevice(&dev));
   RSB_ARG(dev >= 0 && dev < 64, "rsb_jet_render_host: device index %d out of range", dev);
-  std::lock_guard<std::mutex> lock(g_host_mu);
+  std::lock_guard<std::mutex> lock(g_host_mu[dev]);
   HostCtx& cx = g_host_ctx[dev];
   const size_t esz = (flags & RSB_JET_OUT_F64) ? 8 : 4;
   const size_t img_bytes = (size_t)size * size * esz;
@@ -746,6 +746,19 @@ int rsb_jet_render_static(const double* params, const int32_t* zoom_pad, int n, 
       g_static_ptr[dev] = ptr;
     }
     scratch = g_static_ptr[dev];
+  }
+  {
+    // sizes the on-chip renderer takes (up to 256 pixels) need no scratch at all: same kernel as
+    // rsb_jet_render, nothing allocated, the built-in array untouched
+    int cluster = 1;
+    size_t smem = 0;
+    if (v2_supported(size, slots, &cluster, &smem)) {
+      Args a2;
+      a2.params = params; a2.zoom_pad = zoom_pad; a2.n = n; a2.slots = slots; a2.size = size;
+      a2.flags = flags; a2.out = out_img; a2.margin = out_margin; a2.peak = out_peak;
+      a2.scratch = nullptr; a2.pitch = (size + 3) & ~3;
+      return v2_launch(a2, cluster, smem, (cudaStream_t)stream);
+    }
   }
   Plan p;
   if (int e = make_plan(size, &p)) return e;

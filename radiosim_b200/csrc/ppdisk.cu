@@ -9,12 +9,13 @@
 //                   numpy scalar promotes to torch's default dtype), so the same IEEE
 //                   single-precision mul/add/div sequence is issued here without FMA
 //                   contraction.
-//   hconv_kernel  : _smooth/_convolve2d (:398-451) is a CIRCULAR convolution with a
+//   hrun_kernel   : _smooth/_convolve2d (:398-451) is a CIRCULAR convolution with a
 //   vconv_kernel    sum-normalised Gaussian sampled at half-integer offsets; it is separable:
 //                   out[i,j] = sum_kl mask[k,l] h[(i-k+449)%900] h[(j-l+449)%900].  Row pass
-//                   from a shared-memory copy of the byte mask, column pass fused with the
-//                   scale-accumulate over components and the abs (:151-152); only the crop
-//                   the image uses (:154-161) is produced.
+//                   from the RUNS of each mask row and cumulative taps (O(transitions) per
+//                   pixel), column pass from shared-memory tiles (4 x 4 outputs per thread)
+//                   fused with the scale-accumulate over components and the abs (:151-152);
+//                   only the crop the image uses (:154-161) is produced.
 //   resize_kernel : torchvision antialiased bilinear resize (:166-171, ATen
 //                   _upsample_bilinear2d_aa) of the crop + paste into the 1e-10 canvas
 //                   (:178-185), float32 like the reference's output.
@@ -68,79 +69,180 @@ __global__ void __launch_bounds__(256) mask_kernel(const Comp* __restrict__ comp
   }
 }
 
-// Row pass: tmp[c][i][j] = sum_l mask[c][i][l] h[(j-l+449)%900]  for crop rows' SOURCE rows.
-// grid: (rows, components).  h is truncated at +-kReach(sigma) taps (tails < 1e-14).
+// Row pass: tmp[c][i][j] = sum_l mask[c][i][l] h[(j-l+449)%900], taps truncated at +-reach(sigma)
+// (tails < 1e-14).  A mask row is a handful of RUNS (an ellipse row is one interval, a ring row
+// two), so with the cumulative taps G[d] = sum_{u <= d} h[u + 449] a run [l0, l1] contributes
+// G[j - l0] - G[j - l1 - 1]: the pass costs O(transitions) per pixel instead of O(taps), and is
+// summed in float64.  The three terms per transition are the circular wrap (j - t, j - t +- 900).
 __device__ __forceinline__ int reach(int sigma) { return 8 * sigma + 1; }
+constexpr int kMaxReach = 8 * kMaxSigma + 1;
+constexpr int kMaxTrans = 64;  // transitions per mask row kept as a list (more: plain summation)
 
-__global__ void __launch_bounds__(256) hconv_kernel(const Comp* __restrict__ comps,
-                                                    const unsigned char* __restrict__ masks,
-                                                    const float* __restrict__ htab,  // [kMaxSigma+1][900]
-                                                    float* __restrict__ tmp) {
-  __shared__ unsigned char mrow[kFix];
-  __shared__ int any;
-  const Comp c = comps[blockIdx.y];
-  const int i = blockIdx.x;
-  const unsigned char* src = masks + ((size_t)blockIdx.y * kFix + i) * kFix;
-  if (threadIdx.x == 0) any = 0;
-  __syncthreads();
-  int mine = 0;
-  for (int j = threadIdx.x; j < kFix; j += blockDim.x) {
-    const unsigned char m = src[j];
-    mrow[j] = m;
-    mine |= m;
-  }
-  if (mine) any = 1;
-  __syncthreads();
-  float* dst = tmp + ((size_t)blockIdx.y * kFix + i) * kFix;
-  if (!any) {  // empty mask row: zeros
-    for (int j = threadIdx.x; j < kFix; j += blockDim.x) dst[j] = 0.f;
-    return;
-  }
-  const float* h = htab + (size_t)c.sigma * kFix;
-  const int R = reach(c.sigma);
-  for (int j = threadIdx.x; j < kFix; j += blockDim.x) {
-    // taps t = (j - l + 449) % 900 within [449.5 - R, 449.5 + R]  <=>  l = j - d, d = t - 449
-    float s = 0.f;
-    for (int d = -R + 1; d <= R; ++d) {
-      int l = j - d;
-      l += (l < 0) ? kFix : 0;
-      l -= (l >= kFix) ? kFix : 0;
-      s = fmaf((float)mrow[l], h[d + 449], s);
-    }
-    dst[j] = s;
+// gcum[s][k] = sum_{d = -R+1}^{k - R} h_s[d + 449], k = 0 .. 2R (gcum[s][0] = 0), R = reach(s)
+__global__ void gcum_kernel(const float* __restrict__ htab, double* __restrict__ gcum) {
+  const int s = blockIdx.x;
+  if (s < 1 || threadIdx.x != 0) return;
+  const int R = reach(s);
+  double acc = 0.0;
+  double* g = gcum + (size_t)s * (2 * kMaxReach + 1);
+  g[0] = 0.0;
+  for (int k = 1; k <= 2 * R; ++k) {
+    acc += (double)htab[(size_t)s * kFix + (k - R) + 449];
+    g[k] = acc;
   }
 }
 
-// Column pass over the crop + scale-accumulate + abs.
-// grid: (crop column blocks of 128, crop rows, images)
-__global__ void __launch_bounds__(128) vconv_kernel(const Comp* __restrict__ comps,
+// grid: (rows, components); block 128.  Only the crop's columns [lo, hi) are produced.
+__global__ void __launch_bounds__(128) hrun_kernel(const Comp* __restrict__ comps,
+                                                   const Image* __restrict__ images,
+                                                   const unsigned char* __restrict__ masks,
+                                                   const double* __restrict__ gcum,
+                                                   float* __restrict__ tmp) {
+  __shared__ double G[2 * kMaxReach + 1];
+  __shared__ int tpos[kMaxTrans];
+  __shared__ int ntrans;
+  const Comp c = comps[blockIdx.y];
+  const Image im = images[c.image];
+  const int i = blockIdx.x, R = reach(c.sigma), tid = threadIdx.x, lane = tid & 31;
+  const unsigned char* src = masks + ((size_t)blockIdx.y * kFix + i) * kFix;
+  for (int k = tid; k <= 2 * R; k += blockDim.x) G[k] = gcum[(size_t)c.sigma * (2 * kMaxReach + 1) + k];
+  if (tid < 32) {  // warp 0: ordered list of the positions t in [0, 900] where the row changes value
+    int n = 0;
+    for (int j0 = 0; j0 <= kFix; j0 += 32) {
+      const int j = j0 + lane;
+      const int cur = (j < kFix) ? src[j] : 0, prev = (j >= 1 && j <= kFix) ? src[j - 1] : 0;
+      const bool tr = (j <= kFix) && ((cur != 0) != (prev != 0));
+      const unsigned m = __ballot_sync(0xffffffffu, tr);
+      if (tr) {
+        const int pos = n + __popc(m & ((1u << lane) - 1u));
+        if (pos < kMaxTrans) tpos[pos] = j;   // (starts and ends alternate: even entries are starts)
+      }
+      n += __popc(m);
+    }
+    if (lane == 0) ntrans = n;
+  }
+  __syncthreads();
+  float* dst = tmp + ((size_t)blockIdx.y * kFix + i) * kFix;
+  const int n = ntrans;
+  const double total = G[2 * R];
+  if (n <= kMaxTrans) {
+    for (int j = im.lo + tid; j < im.hi; j += blockDim.x) {
+      double s = 0.0;
+      for (int q = 0; q < n; ++q) {
+        const int x = j - tpos[q];   // G index = x + R - ... : G_at(x) = sum_{d <= x} g[d]
+        double v = 0.0;
+#pragma unroll
+        for (int w = -1; w <= 1; ++w) {
+          const int k = x + w * kFix + R;          // k = d + R, g defined for d in (-R, R]
+          v += (k <= 0) ? 0.0 : (k >= 2 * R ? total : G[k]);
+        }
+        s += (q & 1) ? -v : v;
+      }
+      dst[j] = (float)s;
+    }
+  } else {  // a ragged row (never produced by ellipses): plain summation over the taps
+    for (int j = im.lo + tid; j < im.hi; j += blockDim.x) {
+      double s = 0.0;
+      for (int d = -R + 1; d <= R; ++d) {
+        int l = j - d;
+        l += (l < 0) ? kFix : 0;
+        l -= (l >= kFix) ? kFix : 0;
+        if (src[l]) s += G[d + R] - G[d + R - 1];
+      }
+      dst[j] = (float)s;
+    }
+  }
+}
+
+// Column pass over the crop + scale-accumulate + abs:
+//   acc[i][j] = | sum_q scale_q sum_d tmp_q[(i - d) % 900][j] h_q[d + 449] |
+// One CTA per 64 x 64 output tile, 4 x 4 outputs per thread.  Per component the tile's input rows
+// (64 + 2R - 1 of them, circular in the 900 grid) are staged in shared memory; each thread slides down
+// its four columns: one 128-bit load of a staged row and one tap feed sixteen FMAs.
+constexpr int kVT = 64;                                   // tile edge
+constexpr int kVRows = kVT + 2 * kMaxReach;               // staged rows (upper bound)
+__global__ void __launch_bounds__(256) vconv_kernel(const Comp* __restrict__ comps,
                                                     const Image* __restrict__ images,
                                                     const float* __restrict__ htab,
                                                     const float* __restrict__ tmp,
                                                     float* __restrict__ acc) {
+  extern __shared__ __align__(16) float vsm[];
+  float* tile = vsm;                      // [rows][kVT]
+  float* taps = vsm + kVRows * kVT;       // [2R]: taps[k] = h[(k - R + 1) + 449], d = k - R + 1
   const Image im = images[blockIdx.z];
-  const int i = im.lo + blockIdx.y;
-  const int j = im.lo + blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= im.hi || j >= im.hi) return;
-  float core = 0.f, rings = 0.f;
+  const int i0 = im.lo + blockIdx.y * kVT, j0 = im.lo + blockIdx.x * kVT;
+  if (i0 >= im.hi || j0 >= im.hi) return;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int rl0 = ty * 4, cl0 = tx * 4;
+  float core[4][4], rings[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) core[a][b] = rings[a][b] = 0.f;
   for (int q = 0; q < im.ncomp; ++q) {
     const Comp c = comps[im.comp0 + q];
-    const float* h = htab + (size_t)c.sigma * kFix;
+    const int R = reach(c.sigma), nrows = kVT + 2 * R - 1;
     const float* t = tmp + (size_t)(im.comp0 + q) * kFix * kFix;
-    const int R = reach(c.sigma);
-    float s = 0.f;
-    for (int d = -R + 1; d <= R; ++d) {
-      int k = i - d;
+    __syncthreads();  // the previous component's tile is no longer read
+    // staged row p holds grid row (i0 - R + p) mod 900: output row rl uses rows p = rl .. rl + 2R - 1
+    for (int e = tid; e < nrows * (kVT / 4); e += blockDim.x) {
+      const int p = e / (kVT / 4), c4 = (e - p * (kVT / 4)) * 4;
+      int k = i0 - R + p;
       k += (k < 0) ? kFix : 0;
       k -= (k >= kFix) ? kFix : 0;
-      s = fmaf(t[(size_t)k * kFix + j], h[d + 449], s);
+      const float* srow = t + (size_t)k * kFix + j0 + c4;
+      float4 v;
+      v.x = (j0 + c4 + 0 < im.hi) ? srow[0] : 0.f;
+      v.y = (j0 + c4 + 1 < im.hi) ? srow[1] : 0.f;
+      v.z = (j0 + c4 + 2 < im.hi) ? srow[2] : 0.f;
+      v.w = (j0 + c4 + 3 < im.hi) ? srow[3] : 0.f;
+      *reinterpret_cast<float4*>(tile + p * kVT + c4) = v;
+    }
+    for (int k = tid; k < 2 * R; k += blockDim.x) taps[k] = htab[(size_t)c.sigma * kFix + (k - R + 1) + 449];
+    __syncthreads();
+    // out[rl] = sum_{p = rl}^{rl + 2R - 1} tile[p] * g[d],  d = rl + R - p  ->  taps index k = d + R - 1 = rl + 2R - 1 - p
+    float s[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) s[a][b] = 0.f;
+    // step p = rl0 + m, m = 0 .. 2R + 2: row a (rl = rl0 + a) takes tap index ka = a + 2R - 1 - m when 0 <= ka < 2R.
+    // Sliding window of four taps w[a] = taps[a + 2R - 1 - m] (zero outside).
+    float w0 = 0.f, w1 = 0.f, w2 = 0.f, w3 = 0.f;   // taps for rows 0..3 at the current step
+    // at m = 0: ka = a + 2R - 1: only a = 0 is inside
+    const float* trow = tile + rl0 * kVT + cl0;
+    const int steps = 2 * R + 3;
+    for (int m = 0; m < steps; ++m) {
+      // shift: row a at step m uses what row a-1 used at step m-1
+      w3 = w2; w2 = w1; w1 = w0;
+      const int k0 = 2 * R - 1 - m;
+      w0 = (k0 >= 0) ? taps[k0] : 0.f;
+      const float4 v = *reinterpret_cast<const float4*>(trow + m * kVT);
+      s[0][0] = fmaf(v.x, w0, s[0][0]); s[0][1] = fmaf(v.y, w0, s[0][1]); s[0][2] = fmaf(v.z, w0, s[0][2]); s[0][3] = fmaf(v.w, w0, s[0][3]);
+      s[1][0] = fmaf(v.x, w1, s[1][0]); s[1][1] = fmaf(v.y, w1, s[1][1]); s[1][2] = fmaf(v.z, w1, s[1][2]); s[1][3] = fmaf(v.w, w1, s[1][3]);
+      s[2][0] = fmaf(v.x, w2, s[2][0]); s[2][1] = fmaf(v.y, w2, s[2][1]); s[2][2] = fmaf(v.z, w2, s[2][2]); s[2][3] = fmaf(v.w, w2, s[2][3]);
+      s[3][0] = fmaf(v.x, w3, s[3][0]); s[3][1] = fmaf(v.y, w3, s[3][1]); s[3][2] = fmaf(v.z, w3, s[3][2]); s[3][3] = fmaf(v.w, w3, s[3][3]);
     }
     // core in "float64" position, rings summed one after the other into a float32 accumulator
     // (els_full of ppdisks.py:139-149)
-    if (q == 0) core = s * c.scale;
-    else rings = rings + s * c.scale;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        if (q == 0) core[a][b] = s[a][b] * c.scale;
+        else rings[a][b] = rings[a][b] + s[a][b] * c.scale;
+      }
   }
-  acc[((size_t)blockIdx.z * kFix + i) * kFix + j] = fabsf(core + rings);
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int i = i0 + rl0 + a;
+    if (i >= im.hi) continue;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int j = j0 + cl0 + b;
+      if (j < im.hi) acc[((size_t)blockIdx.z * kFix + i) * kFix + j] = fabsf(core[a][b] + rings[a][b]);
+    }
+  }
 }
 
 // Antialiased bilinear resize of acc[lo:hi, lo:hi] to new_size^2 + paste into the canvas.
@@ -211,6 +313,7 @@ int rsb_ppdisk_workspace_bytes(int n_images, int n_comps, size_t* bytes) {
   size_t b = ((size_t)n_comps * px + 255) & ~(size_t)255;  // byte masks
   b += (size_t)n_comps * px * sizeof(float);               // row-pass result
   b += (size_t)n_images * px * sizeof(float);              // accumulated 900 x 900 image
+  b += (size_t)(kMaxSigma + 1) * (2 * kMaxReach + 1) * sizeof(double) + 256;  // cumulative taps
   *bytes = b + 256;
   return 0;
 }
@@ -244,10 +347,15 @@ int rsb_ppdisk_render(const void* comps, int n_comps, const void* images, int n_
   unsigned char* masks = (unsigned char*)workspace;
   float* tmp = (float*)((char*)workspace + (((size_t)n_comps * px + 255) & ~(size_t)255));
   float* acc = tmp + (size_t)n_comps * px;
+  double* gcum = (double*)(((uintptr_t)(acc + (size_t)n_images * px) + 255) & ~(uintptr_t)255);
   if (int e = rsb_ppdisk_masks(comps, n_comps, masks, stream)) return e;
-  hconv_kernel<<<dim3(kFix, n_comps), 256, 0, st>>>((const Comp*)comps, masks, htab_dev, tmp);
+  gcum_kernel<<<kMaxSigma + 1, 32, 0, st>>>(htab_dev, gcum);
   RSB_LAUNCHED();
-  vconv_kernel<<<dim3((kFix + 127) / 128, kFix, n_images), 128, 0, st>>>(
+  hrun_kernel<<<dim3(kFix, n_comps), 128, 0, st>>>((const Comp*)comps, (const Image*)images, masks, gcum, tmp);
+  RSB_LAUNCHED();
+  const size_t vsmem = (size_t)(kVRows * kVT + 2 * kMaxReach) * sizeof(float);
+  RSB_CUDA(cudaFuncSetAttribute(vconv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
+  vconv_kernel<<<dim3((kFix + kVT - 1) / kVT, (kFix + kVT - 1) / kVT, n_images), 256, vsmem, st>>>(
       (const Comp*)comps, (const Image*)images, htab_dev, tmp, acc);
   RSB_LAUNCHED();
   resize_kernel<<<dim3((img_size + 127) / 128, img_size, n_images), 128, 0, st>>>(

@@ -479,7 +479,9 @@ def make_recipes(rng, amount, size, threads=1):
     for kind, ch in enumerate(kids):
         step = max(1, -(-len(ch) // (4 * threads)))
         jobs += [(kind, ch[i : i + step], size) for i in range(0, len(ch), step)]
-    with mp.get_context("fork").Pool(threads) as pool:  # the workers never touch the GPU
+    # "forkserver": the parent may hold a CUDA context and writer threads by now, and forking such a
+    # process is unsafe; the workers only need numpy / scipy and never touch the GPU
+    with mp.get_context("forkserver").Pool(threads) as pool:
         parts = pool.starmap(_packed_chunk, jobs)
     return merge_packed(parts, size)
 

@@ -135,3 +135,29 @@ def test_native_recipes_render_like_the_python_packer():
     assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
     for i in range(90):
         assert np.abs(a[0][i] - b[0][i]).max() <= TOL * b[0][i].max(), i
+
+
+def test_config2_subset_matches_oracle():
+    """BASELINE config 2 (mojave 256^2, class_ratio [1,1,1]): a 300-image bundle, 100 per class, through
+    create_mojave (native recipes) against the oracle's create_mojave on the same generator: labels,
+    coordinates and dates exact, images within 1e-5 of their peak."""
+    from oracle import mojave as om
+    from radiosim_b200.mojave import create_mojave
+
+    conf = SimpleNamespace(general=SimpleNamespace(threads=None),
+                           dataset=SimpleNamespace(img_size=256, bundle_size=300),
+                           mojave=SimpleNamespace(class_ratio=[1, 1, 1]))
+    today = datetime.date(2026, 1, 1)
+    ref, names = om.create_mojave(256, 300, [1, 1, 1], np.random.default_rng(1337), today=today)
+    got, gnames = create_mojave(conf, np.random.default_rng(1337), today=today)
+    assert names == gnames
+    assert np.bincount(ref[1]).tolist() == [100, 100, 100]
+    for k in (1, 2, 3):
+        assert np.array_equal(ref[k], got[k]), names[k]
+    assert [bytes(x) for x in ref[4]] == [bytes(x) for x in got[4]]
+    worst = 0.0
+    for i in range(300):
+        e = np.abs(got[0][i] - ref[0][i]).max() / ref[0][i].max()
+        worst = max(worst, e)
+        assert e <= TOL, (i, int(ref[1][i]), e)
+    print(f"mojave 256^2, 300 images: worst error {worst:.2e} of the image peak")
