@@ -72,10 +72,11 @@ __device__ float swirled(const Blob* blobs, int nb, const float* prof, int N, do
   const double dx = x - c0, dy = y - c0;
   const double rho = sqrt(dx * dx + dy * dy);
   const double rr = radius / 5.0 * 0.6931471805599453;
-  const double theta = strength * exp(-rho / rr) + atan2(dy, dx);
-  double st, ct;
-  sincos(theta, &st, &ct);
-  const double sxp = mirror(c0 + rho * ct, N), syp = mirror(c0 + rho * st, N);
+  // (x0 + rho cos(theta0 + phi), y0 + rho sin(theta0 + phi)) with theta0 = atan2(dy, dx) is the
+  // offset (dx, dy) turned by phi = strength exp(-rho / r'): no atan2, no second rho * cos / sin
+  double sp, cp;
+  sincos(strength * exp(-rho / rr), &sp, &cp);
+  const double sxp = mirror(c0 + (dx * cp - dy * sp), N), syp = mirror(c0 + (dx * sp + dy * cp), N);
   const int x0 = (int)floor(sxp), y0 = (int)floor(syp);
   const float fx = (float)(sxp - x0), fy = (float)(syp - y0);
   const int x1 = min(x0 + 1, N - 1), y1 = min(y0 + 1, N - 1);

@@ -157,23 +157,39 @@ class DeviceSurvey:
         self.flags_jet = L.JET_NORMALIZE if jet_normalize else 0
         # sub-jets sorted by size (CTAs of one wave equally busy); sizes <= 128 take one CTA per
         # image, larger ones a 2-CTA cluster -> two launches at most
+        # ... and anything above 256 pixels (surveys larger than 1310^2) one launch per distinct size
+        # through rsb_jet_render, rows packed without padding
         order = np.argsort(sizes, kind="stable")
         ssz = sizes[order].astype(np.int64)
-        pitch = (ssz + 3) & ~3
+        slots = all_params.shape[1] if nj else 1
+        var_ok = slots <= 32
+        n_var = int(np.searchsorted(ssz, 256, side="right")) if var_ok else 0
+        pitch = np.where(np.arange(nj) < n_var, (ssz + 3) & ~3, ssz)
         pix_sorted = np.zeros(nj, dtype=np.int64)
-        if nj:
-            pix_sorted[1:] = np.cumsum(ssz * pitch)[:-1]      # (multiples of 4: every pitch is)
-        total_pix = int((ssz * pitch).sum())
-        self.groups = []
-        if nj:
-            split = int(np.searchsorted(ssz, 128, side="right"))
-            for a, b in ((0, split), (split, nj)):
+        self.groups, self.big_groups = [], []
+        cursor = 0
+        if n_var:
+            pix_sorted[1:n_var] = np.cumsum((ssz * pitch)[:n_var])[:-1]   # (multiples of 4: every pitch is)
+            cursor = int((ssz * pitch)[:n_var].sum())
+            split = int(np.searchsorted(ssz[:n_var], 128, side="right"))
+            for a, b in ((0, split), (split, n_var)):
                 if b > a:
                     self.groups.append((a, b, int(ssz[b - 1])))
-            if int(ssz[-1]) > 256 or all_params.shape[1] > 32:
-                raise L.RsbError("survey sub-jets larger than 256 pixels or with more than 32 slots "
-                                 "are not supported by the variable-size jet launch")
-        self.slots = all_params.shape[1] if nj else 1
+        need_ws = 0
+        if nj > n_var:
+            big = ssz[n_var:]
+            starts = n_var + np.flatnonzero(np.r_[True, big[1:] != big[:-1]])
+            need = C.c_size_t(0)
+            for a, b in zip(starts, np.r_[starts[1:], nj]):
+                a, b, js = int(a), int(b), int(ssz[a])
+                pix_sorted[a:b] = cursor + np.arange(b - a, dtype=np.int64) * (js * js)
+                self.big_groups.append((a, b, js, cursor))
+                cursor = (cursor + (b - a) * js * js + 3) & ~3      # every group 16-byte aligned
+                L.check(self.lib.rsb_jet_workspace_bytes(b - a, slots, js, C.byref(need)))
+                need_ws = max(need_ws, need.value)
+        total_pix = cursor
+        self.d_jw = L.DeviceBuffer(max(need_ws, 16))
+        self.slots = slots
         rects = np.zeros(max(nj, 1), dtype=JET_RECT)
         jet_offs = np.zeros(n + 1, dtype=np.int32)
         if nj:
@@ -216,6 +232,11 @@ class DeviceSurvey:
                                            self.slots, max_size, self.flags_jet, self.d_pix.ptr,
                                            p_margin + a * 4, p_peak + a * 8, None),
                     "rsb_jet_render_var (survey sub-jets)")
+        for a, b, js, cursor in self.big_groups:
+            L.check(lib.rsb_jet_render(self.p_params + a * self.slots * 48, self.p_zpad + a * 4, b - a,
+                                       self.slots, js, self.flags_jet, self.d_pix.ptr + cursor * 4,
+                                       p_margin + a * 4, p_peak + a * 8, self.d_jw.ptr, self.d_jw.nbytes, None),
+                    "rsb_jet_render (survey sub-jets above 256 pixels)")
         if self.n:
             L.check(lib.rsb_survey_render(self.p_src, self.p_soffs, self.total, self.p_rects,
                                           self.p_joffs, self.d_pix.ptr, self.n, self.size,

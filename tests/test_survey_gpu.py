@@ -71,6 +71,21 @@ def test_survey_config4_source_counts_match_oracle(ns, dist, seed):
     assert abs(float(x.max()) - 1.0) <= 2e-6
 
 
+def test_survey_above_1500_pixels_matches_oracle():
+    """N = 1600: more tiles per image than the GPU has SMs (the tile kernel writes unnormalised planes
+    and a second pass normalises) and sub-jets above 256 pixels (one launch per size through the
+    global-scratch jet kernel)."""
+    from oracle import survey as osur
+    from radiosim_b200.survey import create_survey
+
+    size, ns, dist = 1600, 14, (2, 1, 2)
+    np.random.seed(77)
+    ox, oy = osur.create_survey((1, 3, size, size), ns, dist, True, workers=os.cpu_count() or 1)
+    np.random.seed(77)
+    x, y = create_survey(np.broadcast_to(np.zeros(1), (1, 3, size, size)), _conf(ns, dist))
+    assert np.abs(x - ox).max() <= TOL and np.abs(y - oy).max() <= TOL
+
+
 def test_survey_large_grid_properties():
     """BASELINE config 4 size (1024^2, thousands of sources): oracle-free properties."""
     from radiosim_b200.survey.survey import pack_survey, render_survey
