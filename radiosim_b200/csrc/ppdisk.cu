@@ -92,48 +92,75 @@ __global__ void gcum_kernel(const float* __restrict__ htab, double* __restrict__
   }
 }
 
-// grid: (rows, components); block 128.  Only the crop's columns [lo, hi) are produced.
+// grid: (rows, components); block 128.  Only the crop's columns [lo, hi) are produced, and only the
+// rows the column pass reads (crop rows +- reach, circular).  The mask row is evaluated here (same
+// float32 sequence as mask_kernel: bit-identical) instead of being read back from memory.
 __global__ void __launch_bounds__(128) hrun_kernel(const Comp* __restrict__ comps,
                                                    const Image* __restrict__ images,
-                                                   const unsigned char* __restrict__ masks,
                                                    const double* __restrict__ gcum,
                                                    float* __restrict__ tmp) {
   __shared__ double G[2 * kMaxReach + 1];
+  __shared__ unsigned char mrow[kFix + 4];
+  __shared__ int tlist[4][kMaxTrans / 4];   // transitions found by each warp in its quarter of the row
+  __shared__ int tcount[4];
   __shared__ int tpos[kMaxTrans];
-  __shared__ int ntrans;
   const Comp c = comps[blockIdx.y];
   const Image im = images[c.image];
-  const int i = blockIdx.x, R = reach(c.sigma), tid = threadIdx.x, lane = tid & 31;
-  const unsigned char* src = masks + ((size_t)blockIdx.y * kFix + i) * kFix;
+  const int i = blockIdx.x, R = reach(c.sigma), tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  {
+    int off = i - (im.lo - R);   // position of this row among the rows the column pass reads
+    off += (off < 0) ? kFix : 0;
+    off -= (off >= kFix) ? kFix : 0;
+    if (off >= (im.hi - im.lo) + 2 * R && (im.hi - im.lo) + 2 * R < kFix) return;
+  }
   for (int k = tid; k <= 2 * R; k += blockDim.x) G[k] = gcum[(size_t)c.sigma * (2 * kMaxReach + 1) + k];
-  if (tid < 32) {  // warp 0: ordered list of the positions t in [0, 900] where the row changes value
+  const float dr = (float)(i - kFix / 2);
+  for (int j = tid; j < kFix; j += blockDim.x) {
+    const float dc = (float)(j - kFix / 2);
+    bool m = inside(dr, dc, c.ca, c.sa, c.a2_out, c.b2_out);
+    if (c.a2_in > 0.f) m ^= inside(dr, dc, c.ca, c.sa, c.a2_in, c.b2_in);
+    mrow[j] = m ? 1 : 0;
+  }
+  __syncthreads();
+  {
+    // ordered list of the positions t in [0, 900] where the row changes value: each warp scans a
+    // contiguous quarter (the last one also position 900), the lists are concatenated afterwards
+    const int q0 = warp * 225, q1 = (warp == 3) ? kFix + 1 : q0 + 225;
     int n = 0;
-    for (int j0 = 0; j0 <= kFix; j0 += 32) {
+    for (int j0 = q0; j0 < q1; j0 += 32) {
       const int j = j0 + lane;
-      const int cur = (j < kFix) ? src[j] : 0, prev = (j >= 1 && j <= kFix) ? src[j - 1] : 0;
-      const bool tr = (j <= kFix) && ((cur != 0) != (prev != 0));
+      const int cur = (j < kFix) ? mrow[j] : 0, prev = (j >= 1 && j <= kFix) ? mrow[j - 1] : 0;
+      const bool tr = (j < q1) && (cur != prev);
       const unsigned m = __ballot_sync(0xffffffffu, tr);
       if (tr) {
         const int pos = n + __popc(m & ((1u << lane) - 1u));
-        if (pos < kMaxTrans) tpos[pos] = j;   // (starts and ends alternate: even entries are starts)
+        if (pos < kMaxTrans / 4) tlist[warp][pos] = j;
       }
       n += __popc(m);
     }
-    if (lane == 0) ntrans = n;
+    if (lane == 0) tcount[warp] = n;
+  }
+  __syncthreads();
+  const int n0 = tcount[0], n1 = tcount[1], n2 = tcount[2], n3 = tcount[3];
+  const bool listed = n0 <= kMaxTrans / 4 && n1 <= kMaxTrans / 4 && n2 <= kMaxTrans / 4 && n3 <= kMaxTrans / 4;
+  const int n = n0 + n1 + n2 + n3;
+  if (listed && tid < n) {   // (starts and ends alternate: even entries are starts)
+    const int w = (tid >= n0) + (tid >= n0 + n1) + (tid >= n0 + n1 + n2);
+    const int base = (w > 0 ? n0 : 0) + (w > 1 ? n1 : 0) + (w > 2 ? n2 : 0);
+    tpos[tid] = tlist[w][tid - base];
   }
   __syncthreads();
   float* dst = tmp + ((size_t)blockIdx.y * kFix + i) * kFix;
-  const int n = ntrans;
   const double total = G[2 * R];
-  if (n <= kMaxTrans) {
+  if (listed) {
     for (int j = im.lo + tid; j < im.hi; j += blockDim.x) {
       double s = 0.0;
       for (int q = 0; q < n; ++q) {
-        const int x = j - tpos[q];   // G index = x + R - ... : G_at(x) = sum_{d <= x} g[d]
+        const int x = j - tpos[q];   // G_at(x) = sum_{d <= x} g[d] = G[x + R]
         double v = 0.0;
 #pragma unroll
         for (int w = -1; w <= 1; ++w) {
-          const int k = x + w * kFix + R;          // k = d + R, g defined for d in (-R, R]
+          const int k = x + w * kFix + R;          // g defined for d in (-R, R]
           v += (k <= 0) ? 0.0 : (k >= 2 * R ? total : G[k]);
         }
         s += (q & 1) ? -v : v;
@@ -147,7 +174,7 @@ __global__ void __launch_bounds__(128) hrun_kernel(const Comp* __restrict__ comp
         int l = j - d;
         l += (l < 0) ? kFix : 0;
         l -= (l >= kFix) ? kFix : 0;
-        if (src[l]) s += G[d + R] - G[d + R - 1];
+        if (mrow[l]) s += G[d + R] - G[d + R - 1];
       }
       dst[j] = (float)s;
     }
@@ -348,10 +375,10 @@ int rsb_ppdisk_render(const void* comps, int n_comps, const void* images, int n_
   float* tmp = (float*)((char*)workspace + (((size_t)n_comps * px + 255) & ~(size_t)255));
   float* acc = tmp + (size_t)n_comps * px;
   double* gcum = (double*)(((uintptr_t)(acc + (size_t)n_images * px) + 255) & ~(uintptr_t)255);
-  if (int e = rsb_ppdisk_masks(comps, n_comps, masks, stream)) return e;
+  (void)masks;  // (the mask rows are evaluated inside hrun_kernel; rsb_ppdisk_masks serves callers that want them)
   gcum_kernel<<<kMaxSigma + 1, 32, 0, st>>>(htab_dev, gcum);
   RSB_LAUNCHED();
-  hrun_kernel<<<dim3(kFix, n_comps), 128, 0, st>>>((const Comp*)comps, (const Image*)images, masks, gcum, tmp);
+  hrun_kernel<<<dim3(kFix, n_comps), 128, 0, st>>>((const Comp*)comps, (const Image*)images, gcum, tmp);
   RSB_LAUNCHED();
   const size_t vsmem = (size_t)(kVRows * kVT + 2 * kMaxReach) * sizeof(float);
   RSB_CUDA(cudaFuncSetAttribute(vconv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
