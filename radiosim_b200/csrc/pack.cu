@@ -109,6 +109,13 @@ inline double slot_at(const SlotRot& s, double r, double c) {
   return s.amp * std::exp(-(a * a + b * b) / 2.0);
 }
 
+// upper bound of exp(-q / 2) for a slot's closest approach q to a border line; most slots are far from
+// most lines, and there the bound need not be evaluated: exp(-40) < 4.25e-18
+inline double line_bound(double q) {
+  const double e = 0.5 * q * 0.999999;
+  return e > 40.0 ? 4.25e-18 : std::exp(-e);
+}
+
 // jet.py:149-157: is the maximum of the summed components over the 4(N-1) border pixels
 // below 0.01?  The reference evaluates every border pixel; here two rigorous shortcuts come
 // first and the full evaluation only runs when neither decides:
@@ -148,7 +155,7 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
     const double rows[2] = {0.0, last};
     for (int e = 0; e < 2; ++e) {  // lines r = 0, r = N-1: along the line the column varies
       const double dr = rows[e] - cy, q = dr * dr * det / mcc;
-      const double v = std::fabs(s[k].amp) * std::exp(-0.5 * q * 0.999999);
+      const double v = std::fabs(s[k].amp) * line_bound(q);
       const double t0 = cx - mrc * dr / mcc;
       ls[e][k] = LineSlot{v, t0, mcc * 0.999999};
       upper[e] += v;
@@ -156,7 +163,7 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
     }
     for (int e = 0; e < 2; ++e) {  // lines c = 0, c = N-1: the row varies
       const double dc = rows[e] - cx, q = dc * dc * det / mrr;
-      const double v = std::fabs(s[k].amp) * std::exp(-0.5 * q * 0.999999);
+      const double v = std::fabs(s[k].amp) * line_bound(q);
       const double t0 = cy - mrc * dc / mrr;
       ls[2 + e][k] = LineSlot{v, t0, mrr * 0.999999};
       upper[2 + e] += v;
@@ -257,7 +264,8 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
     if (i >= 1 && g.sample() < 0.1) amp[i] = 0.0;
     if (i >= 2) beta[i] = beta[1] * std::exp(-std::sqrt((double)(i - 1)) * g.normal(0.5, 0.1));
     bend += g.normal(0.0, pi / 24);
-    const double cb = std::cos(bend), sb = std::sin(bend);
+    double cb, sb;
+    sincos(bend, &sb, &cb);
     const double acb = std::fabs(cb), asb = std::fabs(sb);
     const double fill = acb < asb ? 1.0 / asb : (acb > asb ? 1.0 / acb : std::sqrt(2.0));
     const double dist = (double)i / (double)(k - 1) * N / 2 * fill * sin_tilt * 0.7;
@@ -303,8 +311,7 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
     const double* q = p + (size_t)s * 6;
     sr[s].amp = q[0];
     if (q[0] == 0.0) continue;
-    sr[s].cs = std::cos(q[5]);
-    sr[s].sn = std::sin(q[5]);
+    sincos(q[5], &sr[s].sn, &sr[s].cs);
     sr[s].ra = q[2] * sr[s].cs - q[1] * sr[s].sn;
     sr[s].rb = q[2] * sr[s].sn + q[1] * sr[s].cs;
     sr[s].wx = q[3];
