@@ -243,15 +243,23 @@ class DeviceSurvey:
                                           L.JET_OUT_F64 if self.f64 else 0, self.d_x.ptr, self.d_y.ptr,
                                           self.d_w.ptr, self.d_w.nbytes, None), "rsb_survey_render")
 
-    def download_into(self, x: np.ndarray, y: np.ndarray):
+    def download_into(self, x: np.ndarray, y: np.ndarray, copier=None):
         """Asynchronous copies into (page-locked, contiguous) host arrays; ``L.device_sync()`` or a
-        later synchronising call completes them.  Keep this object alive until then."""
+        later synchronising call completes them.  Keep this object alive until then.  With a
+        ``copier`` (:class:`_lib.CopyStream`) the copies run on its stream, behind everything enqueued
+        so far, and overlap whatever the default stream is given next."""
         n, size = self.n, self.size
         assert x.shape == (n, 1, size, size) and y.shape == (n, 4, size, size)
         assert x.dtype == self.dt and y.dtype == self.dt and x.flags.c_contiguous and y.flags.c_contiguous
-        if n:
-            L.check(self.lib.rsb_memcpy_d2h(x.ctypes.data, self.d_x.ptr, x.nbytes, None), "d2h")
-            L.check(self.lib.rsb_memcpy_d2h(y.ctypes.data, self.d_y.ptr, y.nbytes, None), "d2h")
+        if not n:
+            return
+        if copier is not None:
+            copier.after_default()
+            copier.d2h(x, self.d_x.ptr)
+            copier.d2h(y, self.d_y.ptr)
+            return
+        L.check(self.lib.rsb_memcpy_d2h(x.ctypes.data, self.d_x.ptr, x.nbytes, None), "d2h")
+        L.check(self.lib.rsb_memcpy_d2h(y.ctypes.data, self.d_y.ptr, y.nbytes, None), "d2h")
 
     def download(self):
         n, size = self.n, self.size
@@ -295,6 +303,7 @@ def create_survey(grid, conf):
     x = L.pinned_empty((n, 1, size, size), np.float64)
     y = L.pinned_empty((n, 4, size, size), np.float64)
     in_flight = []
+    copier = L.CopyStream.get()
     with ThreadPoolExecutor(1) as ex:
         fut = ex.submit(pack_survey, min(step, n), *args)
         i0 = 0
@@ -305,11 +314,12 @@ def create_survey(grid, conf):
                 fut = ex.submit(pack_survey, min(step, n - i1), *args)
             dev = DeviceSurvey(batch, normalize, f64=True)
             dev.enqueue()
-            dev.download_into(x[i0:i1], y[i0:i1])
+            dev.download_into(x[i0:i1], y[i0:i1], copier)
             in_flight.append(dev)
-            if len(in_flight) > 2:      # bound the device memory held by unfinished chunks
-                L.device_sync()
-                in_flight.clear()
+            if len(in_flight) > 3:      # bound the device memory held by unfinished chunks
+                copier.sync()
+                del in_flight[:-1]
             i0 = i1
+    copier.sync()
     L.device_sync()
     return x, y

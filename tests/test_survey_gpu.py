@@ -32,6 +32,8 @@ def test_create_survey_matches_reference_golden(golden_dir, name):
 
 @pytest.mark.parametrize("size,n,ns,seed,dist", [(128, 3, 20, 5, (2, 1, 2)), (200, 2, 40, 6, (1, 3, 3)),
                                                  (256, 2, 60, 7, (2, 1, 2)), (300, 1, 30, 8, (0, 1, 1)),
+                                                 # sizes that are no multiple of 4 (scalar stores, ragged tiles)
+                                                 (101, 2, 15, 10, (2, 1, 2)), (150, 3, 25, 11, (1, 1, 1)),
                                                  # BASELINE config 4 geometry (1024^2, sub-jets of 100..199 px),
                                                  # with as many sources as the oracle renders in a few seconds
                                                  (1024, 1, 150, 9, (2, 1, 2))])
