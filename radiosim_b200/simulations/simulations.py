@@ -73,6 +73,21 @@ def _noised_sky(sky, conf):
     return out
 
 
+def _bundles_per_call(conf, mode, remaining):
+    """How many bundles one generator call renders.  The jet / survey generators consume the legacy
+    RNG stream image after image, so one call for k * bundle_size images gives exactly the images of k
+    calls for bundle_size -- small bundles (the default TOML: 20 images of 128^2) are rendered several
+    at a time and cut into their shards afterwards.  Not with noise: the reference draws the noise of a
+    bundle before the next bundle's parameters."""
+    if mode not in ("jet", "survey") or (conf.dataset.noise and max(conf.dataset.noise_level) > 0):
+        return 1
+    n, b = conf.dataset.img_size, conf.dataset.bundle_size
+    planes = 1 + (5 if mode == "survey" else 22 if conf.jet.training_type == "gauss" else
+                  1 if conf.jet.training_type == "clean" else 0)
+    per_bundle = b * n * n * 8 * planes
+    return int(max(1, min(remaining, (256 << 20) // max(per_bundle, 1), 4096 // max(b, 1))))
+
+
 def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1):
     """One split: the bundles in ``bundles`` (an iterable of indices) -> one shard each."""
     from ..utils import create_grid
@@ -82,20 +97,23 @@ def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1)
     written = []
     sky = target = data = None
     writer = _ShardWriter()
+    bundles = list(bundles)
+    b = conf.dataset.bundle_size
     try:
-        for i in bundles:
-            path = out / shard_name(mode, opt, i, rank, world)
-            grid = create_grid(conf.dataset.img_size, conf.dataset.bundle_size)
-            if mode == "jet":
-                from ..jets import create_jet
-
-                sky, target = create_jet(grid, conf)
-                writer.submit(path, {"x": _noised_sky(sky, conf), "y": target})
-            elif mode == "survey":
-                from ..survey import create_survey
-
-                sky, target = create_survey(grid, conf)
-                writer.submit(path, {"x": _noised_sky(sky, conf), "y": target})
+        pos = 0
+        while pos < len(bundles):
+            k = _bundles_per_call(conf, mode, len(bundles) - pos)
+            paths = [out / shard_name(mode, opt, i, rank, world) for i in bundles[pos : pos + k]]
+            grid = create_grid(conf.dataset.img_size, b * k)
+            if mode in ("jet", "survey"):
+                if mode == "jet":
+                    from ..jets import create_jet as generate
+                else:
+                    from ..survey import create_survey as generate
+                sky, target = generate(grid, conf)
+                for q, path in enumerate(paths):  # (views of the same page-locked blocks)
+                    writer.submit(path, {"x": _noised_sky(sky[q * b : (q + 1) * b], conf),
+                                         "y": target[q * b : (q + 1) * b]})
             elif mode == "mojave":
                 from ..mojave import create_mojave
 
@@ -104,11 +122,12 @@ def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1)
                     from ..utils import add_noise
 
                     data[0] = add_noise(data[0][:, None], conf.dataset.noise_level)[:, 0]
-                writer.submit(path, dict(zip(names, data)))
+                writer.submit(paths[0], dict(zip(names, data)))
             else:
                 raise ValueError(f"Mode {mode} not found. Choose 'survey', 'jet' or 'mojave' in config file")
             sky = target = data = None  # (the writer holds the only references now)
-            written.append(path)
+            written += paths
+            pos += k
     finally:
         writer.close()
     return written
