@@ -337,6 +337,18 @@ int rsb_add_noise(const double* image_dev, const float* white_dev, const float* 
 int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
                            long long count, float* out);
 
+/* The RNG chain of generate_proto_set / create_proto (reference src/radiosim/ppdisks/ppdisks.py:74-76,
+ * :135, :137, :305, :360-361, :474, :483) on numpy's legacy global stream, in C++ (host only; state
+ * hand-over as rsb_jet_pack): n images -> component and image records for rsb_ppdisk_render.
+ *   cos_tab, sin_tab [alpha_hi] : float32(cos / sin(deg2rad(alpha))) for every integer alpha, computed
+ *     by the caller with numpy (the bit-exact masks are functions of these two numbers)
+ *   comps [comp_cap] 48-byte records, images [n] 32-byte records; *n_comps_out = components written
+ *     (an argument error if they exceed comp_cap; at most about 8 per image). */
+int rsb_ppdisk_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss, int n,
+                    int img_size, int alpha_lo, int alpha_hi, int ratio_lo, int ratio_hi,
+                    double size_ratio_lo, double size_ratio_hi, const float* cos_tab,
+                    const float* sin_tab, void* comps, int comp_cap, void* images, int32_t* n_comps_out);
+
 #ifdef __cplusplus
 }
 #endif

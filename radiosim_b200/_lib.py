@@ -81,6 +81,8 @@ _SIGS = {
     "rsb_noise_workspace_bytes": ([_i32, _i32, C.POINTER(_sz)], _i32),
     "rsb_add_noise": ([_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _sz, _vp], _i32),
     "rsb_legacy_normal_fill": ([_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(C.c_double), C.c_longlong, _vp], _i32),
+    "rsb_ppdisk_pack": ([_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(C.c_double), _i32, _i32, _i32, _i32, _i32,
+                         _i32, C.c_double, C.c_double, _vp, _vp, _vp, _i32, _vp, C.POINTER(_i32)], _i32),
     "rsb_survey_pack": ([_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(C.c_double), _i32, _i32, _i32, _vp, _i32,
                          _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_i32)], _i32),
     "rsb_jet_pack": ([_vp, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(C.c_double), _i32, _i32, _i32, _i32,

@@ -465,3 +465,106 @@ extern "C" int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t
   *cached_gauss = g.gauss;
   return 0;
 }
+
+
+// ---- ppdisk: the RNG chain of generate_proto_set / create_proto ---------------------------
+// reference src/radiosim/ppdisks/ppdisks.py: per image alpha = randint(*alpha_range) (:74), ratio =
+// randint(*ratio_range) / randint(*ratio_range) (:75), size_ratio = uniform(*size_ratio_range) (:76);
+// then create_proto: choice of one of four brightness fits (:474), core a = randint(3, 15) (:305),
+// sc = randint(5, 10) (:135), core scale = exp(m d + n) + normal(0, 0.05 exp(..)) (:477-483),
+// num_circ = floor(normal(3, 0.5)) (:137), per ring randint(10, 35), randint(5, 10), its scale
+// (:360-361, :483); crop and resize target (:154-167).  Same legacy stream and state hand-over as
+// rsb_jet_pack.  cos_tab / sin_tab [alpha_hi]: float32(cos / sin(deg2rad(alpha))) as numpy computes
+// them (the masks are bit-exact functions of these two numbers, so they come from the caller).
+// comps [comp_cap] 48-byte and images [n] 32-byte records as rsb_ppdisk_render takes them.
+namespace rsb {
+namespace pack {
+struct PpComp { float ca, sa, a2_in, b2_in, a2_out, b2_out, scale; int sigma, image, pad[3]; };
+struct PpImage { int comp0, ncomp, lo, hi, new_size, pad[3]; };
+static_assert(sizeof(PpComp) == 48 && sizeof(PpImage) == 32, "ppdisk record layout");
+inline int pp_smooth_factor(double a) { return a < 15 ? 2 : a < 20 ? 4 : a < 30 ? 6 : a < 40 ? 9 : 12; }
+}  // namespace pack
+}  // namespace rsb
+
+extern "C" int rsb_ppdisk_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss, double* cached_gauss,
+                               int n, int img_size, int alpha_lo, int alpha_hi, int ratio_lo, int ratio_hi,
+                               double size_ratio_lo, double size_ratio_hi, const float* cos_tab,
+                               const float* sin_tab, void* comps, int comp_cap, void* images,
+                               int32_t* n_comps_out) {
+  using namespace rsb::pack;
+  RSB_ARG(mt_key && mt_pos && has_gauss && cached_gauss && cos_tab && sin_tab && comps && images && n_comps_out,
+          "rsb_ppdisk_pack: NULL argument");
+  RSB_ARG(n >= 0 && img_size >= 2 && 0 <= alpha_lo && alpha_lo < alpha_hi && 0 < ratio_lo && ratio_lo < ratio_hi,
+          "rsb_ppdisk_pack: bad ranges");
+  RSB_ARG(*mt_pos >= 0 && *mt_pos <= 624, "rsb_ppdisk_pack: generator position %d out of range", *mt_pos);
+  static const double fits[4][2] = {{-0.08908080536281453, -4.808388735775005},
+                                    {-0.04053517757866287, -5.718461569072661},
+                                    {-0.023989028595164514, -6.22105762345096},
+                                    {-0.011198837787046627, -6.701733964123176}};
+  Legacy g{mt_key, *mt_pos, *has_gauss, *cached_gauss};
+  PpComp* C = (PpComp*)comps;
+  PpImage* I = (PpImage*)images;
+  int nc = 0;
+  bool overflow = false;
+  auto push = [&](float ca, float sa, double a2i, double b2i, double a2o, double b2o, double scale, int sigma, int img) {
+    if (nc < comp_cap) {
+      PpComp c;
+      c.ca = ca; c.sa = sa; c.a2_in = (float)a2i; c.b2_in = (float)b2i; c.a2_out = (float)a2o; c.b2_out = (float)b2o;
+      c.scale = (float)scale; c.sigma = sigma; c.image = img; c.pad[0] = c.pad[1] = c.pad[2] = 0;
+      C[nc] = c;
+    } else {
+      overflow = true;
+    }
+    ++nc;
+  };
+  for (int b = 0; b < n; ++b) {
+    const int alpha = (int)g.randint(alpha_lo, alpha_hi);
+    const double r_num = (double)g.randint(ratio_lo, ratio_hi), r_den = (double)g.randint(ratio_lo, ratio_hi);
+    const double ratio = r_num / r_den;
+    const double size_ratio = g.uniform(size_ratio_lo, size_ratio_hi);
+    const int fit = (int)g.randint(0, 4);
+    const double m = fits[fit][0], nn = fits[fit][1];
+    auto scale = [&](double d) {
+      const double e = std::exp(m * d + nn);
+      return e + g.normal(0.0, e * 0.05);
+    };
+    const float ca = cos_tab[alpha], sa = sin_tab[alpha];
+    const double a = (double)g.randint(3, 15);
+    const double bb = a / ratio;
+    const double d_core = (a + bb) / 2;
+    const int sc = (int)g.randint(5, 10);
+    I[b].comp0 = nc;
+    {
+      const double s_core = scale(d_core);
+      push(ca, sa, -1.0, 1.0, a * a, bb * bb, s_core, sc, b);
+    }
+    const int num_circ = (int)std::floor(g.normal(3.0, 0.5));
+    double a_max = d_core;
+    for (int i = 0; i < num_circ; ++i) {
+      const double ra = (double)(g.randint(10, 35) + (i + 1) * 30);
+      const double ex = (double)g.randint(5, 10);
+      const double d_ring = ((ra + ex + (ra + ex) / ratio) / 2 + (ra + ra / ratio) / 2) / 2;
+      const int s = pp_smooth_factor(ra);
+      const double s_ring = scale(d_ring);
+      const double rin = ra / ratio, rout = (ra + ex) / ratio;
+      push(ca, sa, ra * ra, rin * rin, (ra + ex) * (ra + ex), rout * rout, s_ring, s, b);
+      double extent = std::fmax(std::fmax(ra, ra + ex), std::fmax(rin, rout)) + 6 * s;
+      a_max = std::fmax(extent, a_max);
+    }
+    const double half = 450.0;
+    a_max = std::fmin(half, a_max);
+    I[b].ncomp = nc - I[b].comp0;
+    I[b].lo = (int)(half - a_max);
+    I[b].hi = (int)(half + a_max);
+    int nw = (int)(size_ratio * img_size);
+    if (nw % 2) nw -= 1;
+    I[b].new_size = nw;
+    I[b].pad[0] = I[b].pad[1] = I[b].pad[2] = 0;
+  }
+  *n_comps_out = nc;
+  *mt_pos = g.pos;
+  *has_gauss = g.has_gauss;
+  *cached_gauss = g.gauss;
+  RSB_ARG(!overflow, "rsb_ppdisk_pack: %d components do not fit the buffer of %d", nc, comp_cap);
+  return 0;
+}

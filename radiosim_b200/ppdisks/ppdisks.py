@@ -12,6 +12,7 @@ does) and a numpy array otherwise.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -126,6 +127,73 @@ class DeviceProtos:
                 "rsb_ppdisk_render")
 
 
+def pack_protos_native(n, img_size, alpha_range, ratio_range, size_ratio_range):
+    """The RNG chain of ``generate_proto_set`` for ``n`` images natively (``rsb_ppdisk_pack``): component
+    and image records, with the global ``np.random`` stream handed over and back.  ``None`` when a range
+    is not made of integers (numpy then truncates in its own way: the Python packer handles that)."""
+    try:
+        ints = [float(v).is_integer() for v in (*alpha_range, *ratio_range)]
+    except (TypeError, ValueError):
+        return None
+    if not all(ints) or len(alpha_range) != 2 or len(ratio_range) != 2 or len(size_ratio_range) != 2:
+        return None
+    a_lo, a_hi, r_lo, r_hi = (int(v) for v in (*alpha_range, *ratio_range))
+    if not (0 <= a_lo < a_hi <= 100000 and 0 < r_lo < r_hi) or os.environ.get("RSB_PY_PACKER") == "1":
+        return None
+    angles = np.deg2rad(np.arange(a_hi, dtype=np.float64))
+    cos_tab = np.array([np.float32(np.cos(t)) for t in angles], dtype=np.float32)   # scalar calls, as pack_proto
+    sin_tab = np.array([np.float32(np.sin(t)) for t in angles], dtype=np.float32)
+    cap = 12 * max(n, 1) + 64
+    comps = np.zeros(cap, dtype=COMP)
+    images = np.zeros(max(n, 1), dtype=IMAGE)
+    nc = C.c_int32(0)
+    name, key, pos, has_gauss, cached = np.random.get_state()
+    key = np.ascontiguousarray(key, dtype=np.uint32).copy()
+    c_pos, c_has, c_cached = C.c_int32(int(pos)), C.c_int32(int(has_gauss)), C.c_double(float(cached))
+    rc = L.lib().rsb_ppdisk_pack(key.ctypes.data, C.byref(c_pos), C.byref(c_has), C.byref(c_cached), n, img_size,
+                                 a_lo, a_hi, r_lo, r_hi, float(size_ratio_range[0]), float(size_ratio_range[1]),
+                                 cos_tab.ctypes.data, sin_tab.ctypes.data, comps.ctypes.data, cap,
+                                 images.ctypes.data, C.byref(nc))
+    if rc != 0:   # (more components than the buffer holds: left to the Python packer, stream untouched)
+        return None
+    np.random.set_state((name, key, c_pos.value, c_has.value, c_cached.value))
+    return comps[: nc.value], images[:n]
+
+
+def render_records(img_size, comps, images, chunk=64):
+    """Packed records of many images -> float32 ``[n, img_size, img_size]``; chunks of ``chunk`` images,
+    a chunk's copy to the host (second stream) under the next chunk's kernels."""
+    L.require_device()
+    lib = L.lib()
+    n = len(images)
+    out = L.pinned_empty((n, img_size, img_size), np.float32)
+    d_h = L.dev_from(_htab())
+    copier = L.CopyStream.get()
+    keep = []
+    for i0 in range(0, n, chunk):
+        im = images[i0 : i0 + chunk].copy()
+        c0, c1 = int(im["comp0"][0]), int(im["comp0"][-1] + im["ncomp"][-1])
+        cm = comps[c0:c1].copy()
+        cm["image"] -= i0
+        im["comp0"] -= c0
+        need = C.c_size_t(0)
+        L.check(lib.rsb_ppdisk_workspace_bytes(len(im), len(cm), C.byref(need)))
+        d_in, (p_c, p_i), stage = L.upload_blob([cm, im])
+        d_w = L.DeviceBuffer(need.value)
+        d_o = L.DeviceBuffer(len(im) * img_size * img_size * 4)
+        L.check(lib.rsb_ppdisk_render(p_c, len(cm), p_i, len(im), d_h.ptr, img_size, d_o.ptr, d_w.ptr,
+                                      d_w.nbytes, None), "rsb_ppdisk_render")
+        copier.after_default()
+        copier.d2h(out[i0 : i0 + len(im)], d_o.ptr)
+        keep.append((d_in, stage, d_w, d_o))
+        if len(keep) > 3:
+            copier.sync()
+            del keep[:-1]
+    copier.sync()
+    L.device_sync()
+    return out
+
+
 def render_protos(img_size, packed, chunk=32):
     """``packed``: list of ``pack_proto`` results -> float32 ``[n, img_size, img_size]``."""
     L.require_device()
@@ -177,6 +245,12 @@ def generate_proto_set(img_size, size, alpha_range=(0, 180), ratio_range=(3, 15)
                        size_ratio_range=(0.1, 1), device="cuda", seed=1337, verbose=False):
     """Drop-in for ``generate_proto_set`` (``:21-92``): ``(list of float32 arrays, params)``."""
     np.random.seed(seed)                                             # :67
+    params = dict(seed=seed, N=size, img_size=img_size, alpha_range=alpha_range,
+                  ratio_range=ratio_range, size_ratio_range=size_ratio_range)
+    native = pack_protos_native(size, img_size, alpha_range, ratio_range, size_ratio_range) if size else None
+    if native is not None:
+        imgs = render_records(img_size, *native)
+        return [imgs[i] for i in range(size)], params
     packed = []
     for _ in range(size):
         alpha = np.random.randint(*alpha_range)                      # :74
@@ -184,6 +258,4 @@ def generate_proto_set(img_size, size, alpha_range=(0, 180), ratio_range=(3, 15)
         size_ratio = np.random.uniform(*size_ratio_range)            # :76
         packed.append(pack_proto(img_size, alpha, ratio, size_ratio))
     imgs = render_protos(img_size, packed)
-    params = dict(seed=seed, N=size, img_size=img_size, alpha_range=alpha_range,
-                  ratio_range=ratio_range, size_ratio_range=size_ratio_range)
     return [imgs[i] for i in range(size)], params

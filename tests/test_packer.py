@@ -108,3 +108,32 @@ def test_native_survey_packer_continues_the_numpy_stream(n, size, nsrc, dist, sc
     assert np.allclose(a.jet_params, bp, rtol=1e-15, atol=0)
     for u, v in ((a.jet_image, b.jet_image), (a.jet_row0, b.jet_row0), (a.jet_col0, b.jet_col0)):
         assert np.array_equal(u, v)
+
+
+def test_native_ppdisk_packer_matches_python():
+    """rsb_ppdisk_pack against the Python replay of generate_proto_set's chain (ppdisks.py:74-76 +
+    create_proto's draws): stream position equal, integer fields and mask parameters bit-equal, scales
+    to float32 rounding of a last-bit difference in exp()."""
+    from radiosim_b200.ppdisks import ppdisks as pp
+
+    for seed, n, ar, rr, sr in [(42, 300, (0, 180), (3, 15), (0.1, 1.0)), (7, 200, (0.0, 180.0), (3.0, 15.0), (0.5, 1.0)),
+                                (9, 100, (10, 90), (2, 5), (0.1, 0.5))]:
+        np.random.seed(seed)
+        packed = []
+        for _ in range(n):
+            alpha = np.random.randint(*ar)
+            ratio = np.random.randint(*rr) / np.random.randint(*rr)
+            size_ratio = np.random.uniform(*sr)
+            packed.append(pp.pack_proto(512, alpha, ratio, size_ratio))
+        ref_next = np.random.rand()
+        rc, ri = pp._records(packed)
+        np.random.seed(seed)
+        comps, images = pp.pack_protos_native(n, 512, ar, rr, sr)
+        assert np.random.rand() == ref_next
+        assert len(comps) == len(rc) and len(images) == n
+        for f in ("comp0", "ncomp", "lo", "hi", "new_size"):
+            assert np.array_equal(images[f], ri[f]), f
+        for f in ("ca", "sa", "a2_in", "b2_in", "a2_out", "b2_out", "sigma", "image"):
+            assert np.array_equal(comps[f], rc[f]), f
+        assert np.allclose(comps["scale"], rc["scale"], rtol=2e-7, atol=0)
+    assert pp.pack_protos_native(3, 128, (0.5, 180), (3, 15), (0.1, 1)) is None
