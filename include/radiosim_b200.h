@@ -154,7 +154,9 @@ int rsb_jet_render_host(const double* params_host, const int32_t* zoom_pad_host,
  *                 RSB_JET_OUT_F64 (planes: jets, gaussians, points, background)
  *  workspace_dev  >= rsb_survey_workspace_bytes() bytes of device scratch (coefficient records
  *                 and three counters per image; no image-sized scratch: the class planes stay on
- *                 chip until the image maximum is known and are written once, normalised) */
+ *                 chip until the image maximum is known and are written once, normalised)
+ * Calls on different streams of one device are chained (each waits for the previous call's
+ * kernel): the kernel is persistent and sized for the whole GPU. */
 int rsb_survey_workspace_bytes(int n, int size, int total_sources, size_t* bytes);
 int rsb_survey_render(const double* src_params_dev, const int32_t* src_offs_dev,
                       int total_sources, const void* jet_rects_dev, const int32_t* jet_offs_dev,

@@ -312,6 +312,19 @@ __device__ __forceinline__ void store4(OutT* p, bool vec, int valid, float4 v) {
   }
 }
 
+// one thread: wait until every tile of the image has arrived, return the image maximum
+__device__ __noinline__ float wait_image_peak(const unsigned* arrived, const unsigned* peak, unsigned tiles) {
+  const volatile unsigned* arr = arrived;
+  const long long t0 = clock64();
+  while (*arr < tiles) {
+    __nanosleep(64);
+    // (cannot happen by the ticket rule; if it ever does, fail loudly instead of hanging the device)
+    if (clock64() - t0 > 40000000000ll) __trap();
+  }
+  __threadfence();
+  return __uint_as_float(*(const volatile unsigned*)peak);
+}
+
 template <typename OutT>
 __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -330,10 +343,7 @@ __global__ void __launch_bounds__(kThreads, 1) tile_kernel(const TileArgs a) {
     float inv = 1.f;
     if (!a.direct) {
       if (tid == 0) {
-        volatile unsigned* arr = a.arrived + img;
-        while (*arr < (unsigned)a.tiles) __nanosleep(64);
-        __threadfence();
-        sm.inv = 1.f / __uint_as_float(*(volatile unsigned*)(a.peak + img));
+        sm.inv = 1.f / wait_image_peak(a.arrived + img, a.peak + img, (unsigned)a.tiles);
       }
       __syncthreads();
       inv = sm.inv;
@@ -678,6 +688,15 @@ using namespace rsb::splat;
 
 static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
 
+// The CTAs of tile_kernel wait for each other (a tile leaves the chip when its image is complete), which is
+// safe while the kernel owns enough SMs; two such kernels running side by side on different streams could each
+// hold too few.  So tile kernels of one device are chained: each launch waits for the previous one's event.
+#include <mutex>
+namespace {
+std::mutex g_chain_mu;
+cudaEvent_t g_chain_ev[64] = {};
+}  // namespace
+
 extern "C" {
 
 int rsb_survey_workspace_bytes(int n, int size, int total_sources, size_t* bytes) {
@@ -732,6 +751,12 @@ int rsb_survey_render(const double* src_params, const int32_t* src_offs, int tot
   if ((long long)grid > (long long)n * a.tiles) grid = n * a.tiles;
   a.direct = a.tiles > grid ? 1 : 0;
   a.order = order;
+  int dev = 0;
+  RSB_CUDA(cudaGetDevice(&dev));
+  RSB_ARG(dev >= 0 && dev < 64, "rsb_survey_render: device index %d out of range", dev);
+  std::lock_guard<std::mutex> chain(g_chain_mu);   // (held until this call's kernel and event are enqueued)
+  if (!g_chain_ev[dev]) RSB_CUDA(cudaEventCreateWithFlags(&g_chain_ev[dev], cudaEventDisableTiming));
+  else RSB_CUDA(cudaStreamWaitEvent(st, g_chain_ev[dev], 0));
   if (a.direct) {
     identity_order_kernel<<<64, 256, 0, st>>>(a.tiles, ntile, order);
     RSB_LAUNCHED();
@@ -749,6 +774,7 @@ int rsb_survey_render(const double* src_params, const int32_t* src_offs, int tot
     tile_kernel<float><<<grid, kThreads, smem, st>>>(a);
   }
   RSB_LAUNCHED();
+  RSB_CUDA(cudaEventRecord(g_chain_ev[dev], st));
   if (a.direct) {
     int bx = (int)(((size_t)size * size + 255) / 256);
     if (bx > 2048) bx = 2048;
