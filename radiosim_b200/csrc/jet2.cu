@@ -830,6 +830,66 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
       unsigned rest = rc.x;  // slots still to render; the lowest one's coefficients are in q, ct, kk
       float4 qb, cb;
       float2 kb;
+#ifndef RSB_NO_PAIR
+      // Two slots per step: their arithmetic is one straight-line block (both of the four-row-block kind),
+      // so the scheduler has two independent dependency chains per warp to draw from -- with 4 warps per
+      // scheduler the splat is bound by each warp's own chains, not by issue slots.
+      auto blocks_math = [&](const float4& cq, const float4& cc, const float2& ck) {
+        const float d0 = (c0f - cc.z) - cc.w;
+        const f2 d = f2_pack(d0, d0 + 1.f);
+        const f2 Q = f2_mul(f2_pack(cq.y, cq.y), d);
+        const float dr0 = (r0f - cc.x) - cc.y;
+        const f2 Pq = f2_fma(f2_mul(f2_pack(cq.x, cq.x), d), d, f2_pack(cq.w, cq.w));
+        const f2 k2 = f2_pack(ck.x, ck.x), k3 = f2_pack(ck.y, ck.y);
+#pragma unroll
+        for (int b = 0; b < kTileRows; b += 4) {
+          const float dr = dr0 + (float)b;
+          const float Cq = cq.z * dr * dr;
+          const float tw = fmaf(2.f * cq.z, dr, cq.z);
+          float ta, tb, wa, wb;
+          f2_unpack(f2_fma(f2_pack(dr, dr), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
+          f2_unpack(f2_add(Q, f2_pack(tw, tw)), wa, wb);
+          const f2 E0 = f2_pack(P1_EX2(ta), P1_EX2(tb));
+          const f2 U = f2_pack(P1_EX2(fminf(wa, 40.f)), P1_EX2(fminf(wb, 40.f)));
+          const f2 U2 = f2_mul(U, U);
+          acc2[b] = f2_add(acc2[b], E0);
+          acc2[b + 1] = f2_fma(E0, U, acc2[b + 1]);
+          acc2[b + 2] = f2_fma(E0, f2_mul(U2, k2), acc2[b + 2]);
+          acc2[b + 3] = f2_fma(E0, f2_mul(f2_mul(U2, U), k3), acc2[b + 3]);
+        }
+      };
+      while (rest) {
+        rest &= rest - 1;             // (q, ct, kk) hold the slot just removed
+        if (!rest) {
+          __syncwarp();
+          slot_math(q, ct, kk);
+          break;
+        }
+        {
+          const uint32_t an = s_coef + (uint32_t)lowest_bit(rest) * 64u;
+          qb = lds_v4(an);
+          cb = lds_v4(an + 16u);
+          kb = lds_v2(an + 32u);
+        }
+        rest &= rest - 1;
+        const float4 qa = q, ca_ = ct;
+        const float2 ka = kk;
+        {
+          const uint32_t an = s_coef + (uint32_t)max(lowest_bit(rest), 0) * 64u;   // next step's first slot
+          q = lds_v4(an);
+          ct = lds_v4(an + 16u);
+          kk = lds_v2(an + 32u);
+        }
+        __syncwarp();
+        if (ka.x > 0.f && kb.x > 0.f) {
+          blocks_math(qa, ca_, ka);
+          blocks_math(qb, cb, kb);
+        } else {
+          slot_math(qa, ca_, ka);
+          slot_math(qb, cb, kb);
+        }
+      }
+#else
       while (rest) {
         rest &= rest - 1;
         {
@@ -851,6 +911,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
         __syncwarp();
         slot_math(qb, cb, kb);
       }
+#endif
       load_first(nx);  // in flight during the epilogue
       if (c0 + 1 >= N) {  // odd size: the pair's second column lies outside the image
 #pragma unroll
