@@ -33,6 +33,7 @@ int rsb_abi_version(void);
 const char* rsb_last_error(void);
 int rsb_device_count(int* count);
 int rsb_set_device(int device);
+int rsb_get_device(int* device); /* the calling thread's current device */
 int rsb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor,
                     size_t* total_mem);
 int rsb_malloc(void** dev_ptr, size_t bytes);

@@ -39,6 +39,7 @@ _SIGS = {
     "rsb_last_error": ([], C.c_char_p),
     "rsb_device_count": ([C.POINTER(_i32)], _i32),
     "rsb_set_device": ([_i32], _i32),
+    "rsb_get_device": ([C.POINTER(_i32)], _i32),
     "rsb_device_info": ([_i32, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_sz)], _i32),
     "rsb_malloc": ([C.POINTER(_vp), _sz], _i32),
     "rsb_free": ([_vp], _i32),
@@ -146,6 +147,14 @@ _DPOOL_CAP = int(os.environ.get("RSB_DEVICE_POOL_MB", "8192")) << 20
 _CUR_DEV = [0]
 
 
+def current_device() -> int:
+    """The calling thread's current CUDA device (blocks are pooled per device)."""
+    d = _i32(0)
+    if _lib.rsb_get_device(C.byref(d)) != 0:
+        return _CUR_DEV[0]
+    return d.value
+
+
 def _size_class(nbytes: int) -> int:
     """Allocation size for a request: powers of two up to 1 MiB, then multiples of 1/8 of the
     power of two below (at most 12.5 % over-allocation)."""
@@ -171,7 +180,7 @@ class DeviceBuffer:
     def __init__(self, nbytes: int):
         self.nbytes = int(nbytes)
         self._cls = _size_class(nbytes)
-        self._dev = _CUR_DEV[0]
+        self._dev = current_device()
         free = _DPOOL.get((self._dev, self._cls))
         if free:
             self.ptr = free.pop()
@@ -288,7 +297,7 @@ class CopyStream:
 
     @classmethod
     def get(cls):
-        dev = _CUR_DEV[0]
+        dev = current_device()
         if dev not in cls._cache:
             cls._cache[dev] = cls()
         return cls._cache[dev]

@@ -97,6 +97,11 @@ int rsb_memcpy2d_d2h(void* dst, size_t dst_pitch, const void* src, size_t src_pi
                              (cudaStream_t)stream));
   return 0;
 }
+int rsb_get_device(int* device) {
+  RSB_ARG(device != nullptr, "rsb_get_device: NULL out pointer");
+  RSB_CUDA(cudaGetDevice(device));
+  return 0;
+}
 int rsb_stream_create(void** stream) {
   RSB_ARG(stream != nullptr, "rsb_stream_create: NULL out pointer");
   cudaStream_t s;
