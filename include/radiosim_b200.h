@@ -34,6 +34,9 @@ const char* rsb_last_error(void);
 int rsb_device_count(int* count);
 int rsb_set_device(int device);
 int rsb_get_device(int* device); /* the calling thread's current device */
+/* Test aid without a reference counterpart: leaves `pattern` in every SM's shared memory, so that a
+ * test can show a kernel does not depend on what its predecessor left there. */
+int rsb_debug_scrub_shared(unsigned pattern, void* stream);
 int rsb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor,
                     size_t* total_mem);
 int rsb_malloc(void** dev_ptr, size_t bytes);

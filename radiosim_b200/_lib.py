@@ -40,6 +40,7 @@ _SIGS = {
     "rsb_device_count": ([C.POINTER(_i32)], _i32),
     "rsb_set_device": ([_i32], _i32),
     "rsb_get_device": ([C.POINTER(_i32)], _i32),
+    "rsb_debug_scrub_shared": ([C.c_uint, _vp], _i32),
     "rsb_device_info": ([_i32, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_sz)], _i32),
     "rsb_malloc": ([C.POINTER(_vp), _sz], _i32),
     "rsb_free": ([_vp], _i32),

@@ -102,6 +102,25 @@ int rsb_get_device(int* device) {
   RSB_CUDA(cudaGetDevice(device));
   return 0;
 }
+// Test aid: every SM's shared memory is left holding `pattern` (kernels must not depend on what
+// the previous kernel left there; the parity tests run the renderers behind this).
+__global__ void scrub_shared_kernel(unsigned pattern, int words) {
+  extern __shared__ unsigned scrub_words[];
+  for (int i = threadIdx.x; i < words; i += blockDim.x) scrub_words[i] = pattern;
+  __syncthreads();
+  if (scrub_words[(threadIdx.x * 97) % words] != pattern) __trap();  // (keeps the stores alive)
+}
+int rsb_debug_scrub_shared(unsigned pattern, void* stream) {
+  int dev = 0, optin = 0, sms = 0;
+  RSB_CUDA(cudaGetDevice(&dev));
+  RSB_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  RSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  RSB_CUDA(cudaFuncSetAttribute(scrub_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+  // one CTA per SM at a time (the whole opt-in size each); several waves so that none is missed
+  scrub_shared_kernel<<<4 * sms, 256, optin, (cudaStream_t)stream>>>(pattern, optin / 4);
+  RSB_CUDA(cudaGetLastError());
+  return 0;
+}
 int rsb_stream_create(void** stream) {
   RSB_ARG(stream != nullptr, "rsb_stream_create: NULL out pointer");
   cudaStream_t s;

@@ -178,9 +178,12 @@ def test_pipelined_create_jet_equals_single_shot():
     assert np.array_equal(y, source_lists(b, margin, peak, True))
 
 
-def test_variable_size_launch_matches_oracle():
+@pytest.mark.parametrize("scrub", [None, 0xFFFFFFFF])
+def test_variable_size_launch_matches_oracle(scrub):
     """rsb_jet_render_var: jets of many sizes (the sub-jets of a 1024^2 survey: 100..199 px, plus
-    small and 256 px ones) in one launch per cluster shape, each against the oracle."""
+    small and 256 px ones) in one launch per cluster shape, each against the oracle.  Second pass:
+    behind a kernel that leaves NaN bit patterns in every SM's shared memory (tiles the renderer
+    skips are never written; a zero-weight tap on one of them must not turn into NaN)."""
     import ctypes as C
 
     from oracle import jet as ojet
@@ -209,6 +212,8 @@ def test_variable_size_launch_matches_oracle():
         d_p, d_z = L.dev_from(np.array(params)), L.dev_from(np.array(zpads, dtype=np.int32))
         d_s, d_o = L.dev_from(sizes.astype(np.int32)), L.dev_from(offs)
         d_img, d_m, d_k = L.DeviceBuffer(total * 4), L.DeviceBuffer(n * 4), L.DeviceBuffer(n * 8)
+        if scrub is not None:
+            L.check(lib.rsb_debug_scrub_shared(scrub, None))
         L.check(lib.rsb_jet_render_var(d_p.ptr, d_z.ptr, d_s.ptr, d_o.ptr, n, 19, int(sizes.max()),
                                        L.JET_NORMALIZE, d_img.ptr, d_m.ptr, d_k.ptr, None), "rsb_jet_render_var")
         L.device_sync()
@@ -218,3 +223,25 @@ def test_variable_size_launch_matches_oracle():
         for k, sz in enumerate(sizes):
             img = flat[offs[k] : offs[k] + sz * pitch[k]].reshape(sz, pitch[k])[:, :sz]
             assert np.abs(img.astype(np.float64) - refs[k]).max() <= TOL_IMG, (int(sz), k)
+
+
+@pytest.mark.parametrize("size", [64, 100, 128, 157, 200, 224, 255, 256])
+def test_shared_memory_leftovers_do_not_matter(size):
+    """Fixed-size launches behind a kernel that fills shared memory with zeros, NaN and infinity
+    bit patterns: bit-identical images and labels."""
+    from radiosim_b200 import _lib as L
+    from radiosim_b200.jets.packer import pack_jets
+    from radiosim_b200.jets.jet import render_batch
+
+    L.require_device()
+    np.random.seed(77)
+    b = pack_jets(300, size, (3, 10), "normalize")
+    got = []
+    for pattern in (0x0, 0xFFFFFFFF, 0x7F800000):
+        L.check(L.lib().rsb_debug_scrub_shared(pattern, None))
+        img, margin, peak, _ = render_batch(b, True, f64=False)
+        got.append((np.array(img), np.array(margin), np.array(peak)))
+    for img, margin, peak in got:
+        assert np.isfinite(img).all()
+    for img, margin, peak in got[1:]:
+        assert np.array_equal(img, got[0][0]) and np.array_equal(margin, got[0][1]) and np.array_equal(peak, got[0][2])
