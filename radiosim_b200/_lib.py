@@ -146,6 +146,7 @@ _DPOOL: dict = {}         # (device, size class) -> [ptr]
 _DPOOL_BYTES = [0]
 _DPOOL_CAP = int(os.environ.get("RSB_DEVICE_POOL_MB", "8192")) << 20
 _CUR_DEV = [0]
+_POISON = os.environ.get("RSB_POISON_DEVICE_BLOCKS", "0") == "1"
 
 
 def current_device() -> int:
@@ -186,14 +187,16 @@ class DeviceBuffer:
         if free:
             self.ptr = free.pop()
             _DPOOL_BYTES[0] -= self._cls
-            return
-        p = _vp()
-        rc = _lib.rsb_malloc(C.byref(p), self._cls)
-        if rc != 0 and _DPOOL:      # out of memory with blocks cached: give them back and retry
-            device_pool_clear()
+        else:
+            p = _vp()
             rc = _lib.rsb_malloc(C.byref(p), self._cls)
-        check(rc, "rsb_malloc")
-        self.ptr = p.value
+            if rc != 0 and _DPOOL:      # out of memory with blocks cached: give them back and retry
+                device_pool_clear()
+                rc = _lib.rsb_malloc(C.byref(p), self._cls)
+            check(rc, "rsb_malloc")
+            self.ptr = p.value
+        if _POISON:  # test aid: whoever reads a block before writing it gets NaN bit patterns
+            check(_lib.rsb_memset(self.ptr, 0xFF, self._cls, None), "rsb_memset")
 
     def free(self):
         if getattr(self, "ptr", None):

@@ -218,11 +218,18 @@ __global__ void __launch_bounds__(256) vconv_kernel(const Comp* __restrict__ com
       k += (k < 0) ? kFix : 0;
       k -= (k >= kFix) ? kFix : 0;
       const float* srow = t + (size_t)k * kFix + j0 + c4;
+      // rows hrun_kernel did not produce (below the last output row's window: they only meet zero
+      // taps and unstored outputs) are staged as zeros -- 0 x whatever the workspace held is not 0
+      int off = k - (im.lo - R);
+      off += (off < 0) ? kFix : 0;
+      off -= (off >= kFix) ? kFix : 0;
+      const int span = (im.hi - im.lo) + 2 * R;
+      const bool have = off < span || span >= kFix;
       float4 v;
-      v.x = (j0 + c4 + 0 < im.hi) ? srow[0] : 0.f;
-      v.y = (j0 + c4 + 1 < im.hi) ? srow[1] : 0.f;
-      v.z = (j0 + c4 + 2 < im.hi) ? srow[2] : 0.f;
-      v.w = (j0 + c4 + 3 < im.hi) ? srow[3] : 0.f;
+      v.x = (have && j0 + c4 + 0 < im.hi) ? srow[0] : 0.f;
+      v.y = (have && j0 + c4 + 1 < im.hi) ? srow[1] : 0.f;
+      v.z = (have && j0 + c4 + 2 < im.hi) ? srow[2] : 0.f;
+      v.w = (have && j0 + c4 + 3 < im.hi) ? srow[3] : 0.f;
       *reinterpret_cast<float4*>(tile + p * kVT + c4) = v;
     }
     for (int k = tid; k < 2 * R; k += blockDim.x) taps[k] = htab[(size_t)c.sigma * kFix + (k - R + 1) + 449];
