@@ -631,6 +631,9 @@ int grow(void** p, size_t bytes) {
   if (*p) RSB_CUDA(cudaFree(*p));
   *p = nullptr;
   RSB_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+  // test aid (same switch as the Python block pool): NaN bit patterns for whoever reads before writing
+  static const bool poison = [] { const char* e = getenv("RSB_POISON_DEVICE_BLOCKS"); return e && e[0] == '1'; }();
+  if (poison) RSB_CUDA(cudaMemset(*p, 0xFF, bytes ? bytes : 16));
   return 0;
 }
 }  // namespace
