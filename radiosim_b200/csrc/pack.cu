@@ -152,19 +152,22 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
       bounded = false;
       break;
     }
+    // (bounds only: one reciprocal per axis instead of a division per line; the rounding this adds is
+    // ten orders of magnitude inside the 0.999999 factors)
     const double rows[2] = {0.0, last};
+    const double imcc = 1.0 / mcc, imrr = 1.0 / mrr, aamp = std::fabs(s[k].amp);
     for (int e = 0; e < 2; ++e) {  // lines r = 0, r = N-1: along the line the column varies
-      const double dr = rows[e] - cy, q = dr * dr * det / mcc;
-      const double v = std::fabs(s[k].amp) * line_bound(q);
-      const double t0 = cx - mrc * dr / mcc;
+      const double dr = rows[e] - cy, q = dr * dr * det * imcc;
+      const double v = aamp * line_bound(q);
+      const double t0 = cx - mrc * dr * imcc;
       ls[e][k] = LineSlot{v, t0, mcc * 0.999999};
       upper[e] += v;
       if (v > best) { best = v; best_r = rows[e]; best_c = t0; }
     }
     for (int e = 0; e < 2; ++e) {  // lines c = 0, c = N-1: the row varies
-      const double dc = rows[e] - cx, q = dc * dc * det / mrr;
-      const double v = std::fabs(s[k].amp) * line_bound(q);
-      const double t0 = cy - mrc * dc / mrr;
+      const double dc = rows[e] - cx, q = dc * dc * det * imrr;
+      const double v = aamp * line_bound(q);
+      const double t0 = cy - mrc * dc * imrr;
       ls[2 + e][k] = LineSlot{v, t0, mrr * 0.999999};
       upper[2 + e] += v;
       if (v > best) { best = v; best_r = t0; best_c = rows[e]; }
@@ -243,6 +246,13 @@ inline bool border_below(const SlotRot* s, int slots, int size, long long* count
   return !nan && m < thr;
 }
 
+struct SqrtTable {
+  double v[kMaxHi + 2];
+  SqrtTable() {
+    for (int i = 0; i < kMaxHi + 2; ++i) v[i] = std::sqrt((double)i);
+  }
+};
+
 // One image of create_jet's chain (jet.py:54-125 and the draw at :168) on generator g.
 // p [2*hi-1, 6], ex [2*hi-1, 2].
 inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, double* ex, int32_t* zoom_pad,
@@ -252,6 +262,8 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
   const int mid = size / 2;
   double amp[kMaxHi] = {0}, x[kMaxHi] = {0}, y[kMaxHi] = {0}, sx[kMaxHi] = {0}, sy[kMaxHi] = {0},
          rot[kMaxHi] = {0}, beta[kMaxHi] = {0};
+  static const SqrtTable roots;  // sqrt(0 .. kMaxHi), the same correctly rounded values std::sqrt returns
+  const double* root = roots.v;
   const int k = (int)g.randint(comp_lo, (int64_t)hi + 1);
   rot[0] = g.uniform(0.0, pi);
   const double beta1 = g.uniform(0.0, 1.0);
@@ -260,9 +272,9 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
   const double tilt = g.uniform(0.0, pi / 2);
   const double sin_tilt = std::sin(tilt);
   for (int i = 0; i < k; ++i) {
-    amp[i] = std::exp(-std::sqrt((double)i) * g.normal(1.3, 0.2));
+    amp[i] = std::exp(-root[i] * g.normal(1.3, 0.2));
     if (i >= 1 && g.sample() < 0.1) amp[i] = 0.0;
-    if (i >= 2) beta[i] = beta[1] * std::exp(-std::sqrt((double)(i - 1)) * g.normal(0.5, 0.1));
+    if (i >= 2) beta[i] = beta[1] * std::exp(-root[i - 1] * g.normal(0.5, 0.1));
     bend += g.normal(0.0, pi / 24);
     double cb, sb;
     sincos(bend, &sb, &cb);
@@ -271,7 +283,7 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
     const double dist = (double)i / (double)(k - 1) * N / 2 * fill * sin_tilt * 0.7;
     x[i] = dist * cb + mid;
     y[i] = dist * sb + mid;
-    const double num = N / (double)k * fill * std::sqrt((double)(i + 1));
+    const double num = N / (double)k * fill * root[i + 1];
     const double p0 = num / g.uniform(3.0, 8.0), p1 = num / g.uniform(3.0, 8.0);
     if (p0 >= p1) { sx[i] = p0; sy[i] = p1; } else { sx[i] = p1; sy[i] = p0; }
     if (i >= 1) rot[i] = rot[i - 1] + g.normal(0.0, pi / 18);
@@ -282,9 +294,13 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
   std::memset(ex, 0, sizeof(double) * slots * 2);
   double away[kMaxHi];
   for (int i = 0; i < hi; ++i) {
-    const double lorentz = 1.0 / std::sqrt(1.0 - beta[i] * beta[i]);
-    const double toward = 1.0 / (lorentz * (1.0 - beta[i] * mu));
-    away[i] = 1.0 / (lorentz * (1.0 + beta[i] * mu));
+    double toward = 1.0;  // (beta = 0: the expressions below give exactly 1)
+    away[i] = 1.0;
+    if (beta[i] != 0.0) {
+      const double lorentz = 1.0 / std::sqrt(1.0 - beta[i] * beta[i]);
+      toward = 1.0 / (lorentz * (1.0 - beta[i] * mu));
+      away[i] = 1.0 / (lorentz * (1.0 + beta[i] * mu));
+    }
     p[i * 6 + 0] = amp[i] * toward;
     p[i * 6 + 1] = x[i] + off_x;
     p[i * 6 + 2] = y[i] + off_y;
@@ -311,7 +327,13 @@ inline void pack_one_jet(Legacy& g, int size, int comp_lo, int hi, double* p, do
     const double* q = p + (size_t)s * 6;
     sr[s].amp = q[0];
     if (q[0] == 0.0) continue;
-    sincos(q[5], &sr[s].sn, &sr[s].cs);
+    const int twin = s - hi + 1;  // a counter-jet slot has the rotation of its forward twin
+    if (s >= hi && sr[twin].amp != 0.0) {
+      sr[s].sn = sr[twin].sn;
+      sr[s].cs = sr[twin].cs;
+    } else {
+      sincos(q[5], &sr[s].sn, &sr[s].cs);
+    }
     sr[s].ra = q[2] * sr[s].cs - q[1] * sr[s].sn;
     sr[s].rb = q[2] * sr[s].sn + q[1] * sr[s].cs;
     sr[s].wx = q[3];
