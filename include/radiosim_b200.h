@@ -241,6 +241,12 @@ int rsb_mojave_pack(const uint32_t* entropy, int n_entropy, const uint32_t* spaw
  *   blobs_out_dev [n_blobs] 16-byte records, profiles_out_dev [n_blobs][2][size] float32 */
 int rsb_mojave_blobs(const void* recipes_dev, int n, const void* blob_params_dev, int n_blobs, int size,
                      void* blobs_out_dev, float* profiles_out_dev, void* stream);
+/* add_swirl's image operation (mojave.py:259: skimage.transform.swirl(jet, center=, strength=, radius=),
+ * other arguments at scikit-image's defaults: rotation 0, order 1, mode 'reflect', clip) on an arbitrary
+ * float64 image in device memory.  center = (x, y) = (column, row); [clip_lo, clip_hi] = the input's
+ * minimum and maximum.  Not in place. */
+int rsb_swirl(const double* image_dev, int rows, int cols, double center_x, double center_y, double strength,
+              double radius, double clip_lo, double clip_hi, double* out_dev, void* stream);
 /* For tests: PCG64 (state, inc) of spawned children as numpy reports them, and raw draws of one
  * Generator method from such a state (kind 0 random, 1 standard_normal, 2 standard_exponential,
  * 3 power(a), 4 integers(a, b), 5 uniform(a, b)); state4 = {state hi, state lo, inc hi, inc lo}. */

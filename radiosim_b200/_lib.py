@@ -75,6 +75,7 @@ _SIGS = {
     "rsb_mojave_render": ([_vp, _i32, _vp, _vp, _i32, _u32, _vp, _vp, _sz, _vp], _i32),
     "rsb_mojave_pack": ([_vp, _i32, _vp, _i32, C.c_longlong, _i32, _vp, _i32, _vp, _vp, _i32, C.POINTER(_i32)], _i32),
     "rsb_mojave_blobs": ([_vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp], _i32),
+    "rsb_swirl": ([_vp, _i32, _i32, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _vp, _vp], _i32),
     "rsb_pcg64_spawn_states": ([_vp, _i32, _vp, _i32, C.c_longlong, _i32, _vp], _i32),
     "rsb_pcg64_draws": ([_vp, _i32, C.c_double, C.c_double, _i32, _vp], _i32),
     "rsb_source_margin": ([_vp, _i32, C.c_double, _vp, _vp], _i32),

@@ -257,6 +257,30 @@ __global__ void __launch_bounds__(256) fin_kernel(const Recipe* __restrict__ rec
   }
 }
 
+// skimage.transform.swirl of an ARBITRARY float64 image (add_swirl as a stand-alone drop-in; the bundle
+// path swirls analytically inside pre_kernel).  Same restatement as `swirled` above: inverse map, the
+// offset vector turned by strength * exp(-rho / r'), ndimage 'mirror' boundary, order-1 interpolation in
+// float64, result clipped to the input's range [lo, hi].  grid: (column blocks, rows)
+__global__ void __launch_bounds__(256) swirl_image_kernel(const double* __restrict__ in, int rows, int cols,
+                                                          double cx, double cy, double strength, double radius,
+                                                          double lo, double hi, double* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= cols) return;
+  const double dx = x - cx, dy = y - cy;
+  const double rho = sqrt(dx * dx + dy * dy);
+  const double rr = radius / 5.0 * 0.6931471805599453;
+  double sp, cp;
+  sincos(strength * exp(-rho / rr), &sp, &cp);
+  const double sxp = mirror(cx + (dx * cp - dy * sp), cols), syp = mirror(cy + (dx * sp + dy * cp), rows);
+  const int x0 = (int)floor(sxp), y0 = (int)floor(syp);
+  const double fx = sxp - x0, fy = syp - y0;
+  const int x1 = min(x0 + 1, cols - 1), y1 = min(y0 + 1, rows - 1);  // (weight 0 when clamped)
+  const double v00 = in[(size_t)y0 * cols + x0], v01 = in[(size_t)y0 * cols + x1];
+  const double v10 = in[(size_t)y1 * cols + x0], v11 = in[(size_t)y1 * cols + x1];
+  const double v = (1.0 - fy) * ((1.0 - fx) * v00 + fx * v01) + fy * ((1.0 - fx) * v10 + fx * v11);
+  out[(size_t)y * cols + x] = fmin(fmax(v, lo), hi);
+}
+
 }  // namespace mojave
 }  // namespace rsb
 
@@ -279,6 +303,17 @@ int rsb_mojave_blobs(const void* recipes, int n, const void* blob_params, int n_
   RSB_ARG(recipes && blob_params && blobs_out && profiles_out, "rsb_mojave_blobs: NULL buffer");
   blob_kernel<<<2 * n, 256, 0, (cudaStream_t)stream>>>((const Recipe*)recipes, (const BlobParam*)blob_params, size,
                                                      (Blob*)blobs_out, profiles_out);
+  RSB_LAUNCHED();
+  return 0;
+}
+
+int rsb_swirl(const double* image_dev, int rows, int cols, double center_x, double center_y, double strength,
+              double radius, double clip_lo, double clip_hi, double* out_dev, void* stream) {
+  RSB_ARG(rows >= 1 && cols >= 1 && rows <= 65535, "rsb_swirl: bad shape (%d, %d)", rows, cols);
+  RSB_ARG(image_dev && out_dev && image_dev != out_dev, "rsb_swirl: NULL buffer or in-place call");
+  RSB_ARG(radius != 0.0, "rsb_swirl: radius must not be zero");
+  swirl_image_kernel<<<dim3((cols + 255) / 256, rows), 256, 0, (cudaStream_t)stream>>>(
+      image_dev, rows, cols, center_x, center_y, strength, radius, clip_lo, clip_hi, out_dev);
   RSB_LAUNCHED();
   return 0;
 }

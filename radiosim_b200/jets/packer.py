@@ -65,16 +65,23 @@ def border_max(p6: np.ndarray, size: int, coords=None) -> float:
     return np.sum(planes, axis=0).max()
 
 
-def _mojave_flux():
-    """One draw of the MOJAVE peak-flux fit (``jets/flux_scaling.py:6-20``)."""
+def draw_from_mojave_dist():
+    """``jets/flux_scaling.py:12-20``: one draw (legacy global stream, through scipy) of the beta fit to
+    the MOJAVE archive's peak fluxes."""
     from scipy import stats
 
-    return (
-        stats.beta(
-            0.8639672251677816, 47.64189171625089, 0.09163404776954732, 1892.3881692069087
-        ).rvs(1)
-        / 1e3
-    )
+    return stats.beta(0.8639672251677816, 47.64189171625089, 0.09163404776954732, 1892.3881692069087).rvs(1)
+
+
+def get_start_amp(scale_type):
+    """``jets/flux_scaling.py:6-9`` (any other ``scale_type`` raises ``UnboundLocalError`` there too)."""
+    if scale_type == "mojave":
+        amp_start = draw_from_mojave_dist()
+    return amp_start / 1e3
+
+
+def _mojave_flux():
+    return get_start_amp("mojave")
 
 
 def pack_jets(n: int, size: int, num_jet_components=(3, 10), scaling="normalize") -> JetBatch:

@@ -1,3 +1,5 @@
-from .mojave import create_mojave, gen_compact, gen_one_jet, gen_two_jet
+from .mojave import (add_swirl, create_mojave, gen_compact, gen_jet, gen_one_jet, gen_shocks, gen_two_jet,
+                     swirl_image)
 
-__all__ = ["create_mojave", "gen_compact", "gen_one_jet", "gen_two_jet"]
+__all__ = ["add_swirl", "create_mojave", "gen_compact", "gen_jet", "gen_one_jet", "gen_shocks", "gen_two_jet",
+           "swirl_image"]

@@ -437,13 +437,71 @@ def gen_jet(size, amplitude, width, length, a):
     return render_sources([s], size)[0]
 
 
-def gen_shocks(*args, **kwargs):  # pragma: no cover - kept for API completeness
-    raise NotImplementedError("gen_shocks operates on host images in the reference; here shocks "
-                              "are part of the recipe (see _add_shocks)")
+def gen_shocks(jet, shock_comp, length, width, sx, rng):
+    """``gen_shocks`` ``:124-219`` on a host image, as the reference's signature has it: equally spaced
+    shocks (each a device-rendered ``skewed_gauss``) added to ``jet`` IN PLACE; returns ``(jet,
+    printout_information, skipped)``.  Same draws in the same order from ``rng``; an out-of-range
+    position is passed over before its amplitude factor is drawn, as the reference's ``IndexError``
+    handler does.  (The bundle path does not come through here: there the shocks are blobs of the
+    recipe, ``_add_shocks``.)"""
+    from ..utils.gauss import skewed_gauss
+
+    info = ([], [], [], [], [], [], [], [], [])
+    size = len(jet)
+    step = (2 * length - sx) / shock_comp
+    dist = step
+    skipped = 0
+    for _ in range(shock_comp):
+        if rng.uniform(0, 1) > 2 / 3:
+            skipped += 1
+            continue
+        s_x, s_y = size / 2 + dist, size / 2
+        try:
+            at = jet[int(s_y), int(s_x)]
+        except IndexError:
+            continue
+        s_amp = at * rng.uniform(0.03, 0.6)
+        s_sx = rng.uniform(*np.sort([2, width]))
+        s_sy = rng.uniform(*np.sort([s_sx, length / shock_comp]))
+        s_a = rng.uniform(5, 9)
+        jet += skewed_gauss(size, int(s_x), int(s_y), s_amp, s_sx, s_sy, s_a)   # (float32 render: values below 1e-8 come back as 0)
+        for lst, v in zip(info, ("r", s_amp, int(s_x), int(s_y), s_sx, s_sy, 0, dist, s_a)):
+            lst.append(v)
+        dist += step
+    return jet, info, skipped
 
 
-def add_swirl(*args, **kwargs):  # pragma: no cover
-    raise NotImplementedError("add_swirl is fused into rsb_mojave_render; see _swirl")
+def swirl_image(image, center, strength, radius):
+    """``skimage.transform.swirl(image, center=center, strength=strength, radius=radius)`` (all other
+    arguments at their defaults) on the device: ``rsb_swirl``."""
+    from .. import _lib as L
+
+    L.require_device()
+    img = np.ascontiguousarray(image, dtype=np.float64)
+    if img.ndim != 2:
+        raise ValueError("swirl_image: a 2-D image is expected")
+    rows, cols = img.shape
+    d_in = L.dev_from(img)
+    d_out = L.DeviceBuffer(max(img.nbytes, 16))
+    L.check(L.lib().rsb_swirl(d_in.ptr, rows, cols, float(center[0]), float(center[1]), float(strength),
+                              float(radius), float(img.min()), float(img.max()), d_out.ptr, None), "rsb_swirl")
+    return np.array(d_out.download((rows, cols), np.float64))
+
+
+def add_swirl(jet, rng, first_jet_params=None):
+    """``add_swirl`` ``:222-261``: draws the swirl (or varies the first jet's by ~10 %) and applies it;
+    returns ``(swirled_jet, (strength, radius, center))``."""
+    size = len(jet)
+    if not first_jet_params:
+        strength = rng.normal(loc=0, scale=0.2)
+        radius = rng.uniform(50, 200)
+        center = np.array([size / 2, size / 2])
+    else:
+        deviation = 1 + rng.normal(loc=0, scale=0.1, size=2)
+        strength = first_jet_params[0] * deviation[0]
+        radius = first_jet_params[1] * deviation[1]
+        center = first_jet_params[2]
+    return swirl_image(jet, center, strength, radius), (strength, radius, center)
 
 
 def class_counts(class_ratio, bundle_size):

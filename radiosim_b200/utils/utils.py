@@ -7,8 +7,9 @@ import numpy as np
 from .. import _lib as L
 from ..h5min import write_h5
 
-__all__ = ["create_grid", "pol2cart", "relativistic_boosting", "save_sky_distribution_bundle",
-           "zoom_on_source", "zoom_out"]
+__all__ = ["cart2pol", "create_grid", "load_data", "pol2cart", "relativistic_boosting",
+           "save_sky_distribution_bundle", "zoom_on_source", "zoom_out", "_gen_date",
+           "_gen_vlba_obs_position", "_save_mojave_bundle"]
 
 
 class _ShapeOnly:
@@ -41,6 +42,32 @@ def relativistic_boosting(theta, beta):
 def pol2cart(r, phi):
     """``utils.py:433-454``."""
     return (r * np.cos(phi), r * np.sin(phi))
+
+
+def cart2pol(x, y):
+    """``utils.py:409-430``."""
+    return (np.sqrt(x**2 + y**2), np.arctan2(y, x))
+
+
+def _gen_vlba_obs_position(rng, size):
+    """``utils.py:386-390``: RA in [0, 360), DEC in [-30, 87), in this order from ``rng``."""
+    ra = rng.uniform(0, 360, size=size)
+    dec = rng.uniform(-30, 87, size=size)
+    return ra, dec
+
+
+def _gen_date(rng, start_date, size, today=None):
+    """``utils.py:393-406``: uniformly drawn days between ``start_date`` and today as fixed-length
+    10-byte strings (what h5py's ``string_dtype("utf-8", 10)`` stores).  ``today`` can be frozen for
+    reproducible bundles."""
+    start = np.datetime64(start_date)
+    if today is None:
+        from datetime import datetime
+
+        today = datetime.now().date()
+    delta = np.datetime64(today) - start
+    dates = start + rng.integers(delta.astype(int), size=size)
+    return dates.astype("S10")
 
 
 def _resize(planes: np.ndarray, crop: int, dst: int, pad: int) -> np.ndarray:
@@ -87,3 +114,30 @@ def zoom_out(img, comp=None, pad_value=0):
 def save_sky_distribution_bundle(path, x, y, name_x="x", name_y="y"):
     """``utils.py:344-364`` through the built-in HDF5 writer (no h5py on this image)."""
     write_h5(path, {name_x: np.asarray(x), name_y: np.asarray(y)})
+
+
+def _save_mojave_bundle(path, data, data_name):
+    """``utils.py:367-383``: one dataset per (array, name) pair."""
+    assert len(data) == len(data_name)
+    write_h5(path, {name: np.asarray(dat) for dat, name in zip(data, data_name)})
+
+
+def load_data(conf_path, data_type="train", key="x"):
+    """``utils.py:457-470``: every image of dataset ``key`` from the bundles of one split under the
+    configuration's ``paths.outpath`` (the reference's pattern ``"data*" + data_type`` as a regular
+    expression on the file name -- which, as in the reference, matches ``datatrain...`` but not the
+    writer's own ``data_jet_train_0.h5``), through the built-in HDF5 reader."""
+    import re
+    import tomllib
+    from pathlib import Path
+
+    from ..h5min import read_h5
+
+    with open(conf_path, "rb") as f:
+        config = tomllib.load(f)
+    path = Path(config["paths"]["outpath"])
+    data = []
+    for p in path.iterdir():
+        if re.findall("data*" + data_type, p.name):
+            data.extend(read_h5(p)[key])
+    return data

@@ -150,3 +150,59 @@ def test_mojave_direct_draws_equal_scipy():
             assert skewnorm.rvs(a, loc, scale, random_state=r1) == _skewnorm_rvs(r2, a, loc, scale)
         assert expon.rvs(1.715e-4, 1.985e-2, random_state=r1) == _expon_rvs(r2, 1.715e-4, 1.985e-2)
     assert r1.random() == r2.random()
+
+
+def test_small_helpers_of_the_reference_utils(tmp_path):
+    """cart2pol / pol2cart, the VLBA position and date draws (utils.py:386-454), get_start_amp
+    (jets/flux_scaling.py) and load_data (utils.py:457-470) through the built-in HDF5 reader."""
+    import datetime
+
+    from radiosim_b200 import utils as u
+    from radiosim_b200.h5min import write_h5
+    from radiosim_b200.jets import draw_from_mojave_dist, get_start_amp
+    from radiosim_b200.utils.utils import _gen_date, _gen_vlba_obs_position, _save_mojave_bundle
+
+    r, phi = u.cart2pol(3.0, -4.0)
+    assert r == 5.0 and phi == np.arctan2(-4.0, 3.0)
+    x, y = u.pol2cart(r, phi)
+    assert abs(x - 3.0) < 1e-15 and abs(y + 4.0) < 1e-15
+
+    a, b = np.random.default_rng(5), np.random.default_rng(5)
+    ra, dec = _gen_vlba_obs_position(a, 7)
+    assert np.array_equal(ra, b.uniform(0, 360, size=7)) and np.array_equal(dec, b.uniform(-30, 87, size=7))
+    today = datetime.date(2024, 5, 17)
+    d = _gen_date(a, "1995-01-01", 4, today=today)
+    days = (np.datetime64(today) - np.datetime64("1995-01-01")).astype(int)
+    want = (np.datetime64("1995-01-01") + b.integers(days, size=4)).astype("S10")
+    assert d.dtype == np.dtype("S10") and np.array_equal(d, want)
+
+    from scipy import stats
+    np.random.seed(11)
+    amp = get_start_amp("mojave")
+    np.random.seed(11)
+    ref = stats.beta(0.8639672251677816, 47.64189171625089, 0.09163404776954732, 1892.3881692069087).rvs(1) / 1e3
+    assert np.array_equal(amp, ref) and draw_from_mojave_dist().shape == (1,)
+    with pytest.raises(UnboundLocalError):
+        get_start_amp("normalize")
+
+    out = tmp_path / "build"
+    out.mkdir()
+    rng = np.random.default_rng(2)
+    bundles = {}
+    for split, count in (("train", 2), ("valid", 1)):
+        for i in range(count):
+            xs = rng.random((3, 1, 8, 8))
+            bundles[(split, i)] = xs
+            write_h5(out / f"data_jet_{split}_{i}.h5", {"x": xs, "y": rng.random((3, 19, 8))})
+    _save_mojave_bundle(out / "other.h5", (np.arange(3.0),), ("galaxies",))
+    conf = tmp_path / "c.toml"
+    conf.write_text(f'[paths]\noutpath = "{out}"\n')
+    # the reference's pattern "data*" + data_type is a REGULAR EXPRESSION ("dat", any number of "a", then the
+    # split name), so it does not match the writer's own "data_jet_train_0.h5"; replicated as it is
+    assert u.load_data(conf, "train", "x") == []
+    for (split, i), xs in bundles.items():
+        write_h5(out / f"data{split}_{i}.h5", {"x": xs})
+    got = u.load_data(conf, "train", "x")
+    assert len(got) == 6
+    assert any(np.array_equal(got[0], w[0]) for w in (bundles[("train", 0)], bundles[("train", 1)]))
+    assert len(u.load_data(conf, "valid", "x")) == 3

@@ -161,3 +161,83 @@ def test_config2_subset_matches_oracle():
         worst = max(worst, e)
         assert e <= TOL, (i, int(ref[1][i]), e)
     print(f"mojave 256^2, 300 images: worst error {worst:.2e} of the image peak")
+
+
+def test_gen_jet_and_gen_shocks_standalone_match_oracle():
+    """``gen_jet`` / ``gen_shocks`` with the reference's signatures on host images
+    (mojave.py:84-219): same draws, images within 1e-5 of the jet's peak."""
+    from oracle import mojave as om
+    from radiosim_b200 import mojave as m
+
+    for seed, size, comp in ((3, 256, 5), (4, 200, 8), (5, 128, 3), (6, 96, 6)):
+        amp, width, length, a, sx = 3.0, 6.0 + seed, size / 5, 4.0, 5.0
+        ref = om.base_jet(size, amp, width, length, a)
+        jet = m.gen_jet(size, amp, width, length, a)
+        assert jet.shape == ref.shape and jet.dtype == np.float64
+        assert np.abs(jet - ref).max() <= TOL * ref.max()
+        r_o, r_g = np.random.default_rng(seed), np.random.default_rng(seed)
+        ref2 = om.add_shocks(ref.copy(), comp, length, width, sx, r_o)
+        out, info, skipped = m.gen_shocks(ref.copy(), comp, length, width, sx, r_g)
+        assert r_o.random() == r_g.random()                       # same number of draws
+        assert np.abs(out - ref2).max() <= TOL * ref2.max()
+        assert len(info) == 9 and all(len(col) == len(info[0]) for col in info)
+        assert 0 <= skipped <= comp and len(info[0]) + skipped <= comp
+        assert all(o == "r" for o in info[0]) and all(rot == 0 for rot in info[6])
+
+
+def test_gen_shocks_out_of_range_position_draws_nothing_more():
+    """A shock position outside the image is passed over before its amplitude factor is drawn
+    (the reference's ``IndexError`` handler, mojave.py:189-192)."""
+    from oracle import mojave as om
+    from radiosim_b200 import mojave as m
+
+    size = 64
+    jet = om.base_jet(size, 2.0, 4.0, 20.0, 3.0)
+    for seed in range(4):
+        r_o, r_g = np.random.default_rng(seed), np.random.default_rng(seed)
+        ref = om.add_shocks(jet.copy(), 4, 200.0, 5.0, 3.0, r_o)      # step ~ 100 px: beyond the image
+        out, info, skipped = m.gen_shocks(jet.copy(), 4, 200.0, 5.0, 3.0, r_g)
+        assert r_o.random() == r_g.random()
+        assert np.abs(out - ref).max() <= TOL * ref.max()
+        assert len(info[0]) == 0
+
+
+@pytest.mark.parametrize("shape", [(256, 256), (128, 200), (97, 61)])
+def test_swirl_image_matches_oracle_and_known_answers(shape):
+    """``rsb_swirl`` against the restated scikit-image swirl (PARITY UNPINNED like the fused path)
+    plus what needs no pin: strength 0 is the identity, and the result stays inside the input's range."""
+    from oracle import warps
+    from radiosim_b200.mojave import swirl_image
+
+    rng = np.random.default_rng(8)
+    img = rng.random(shape) ** 3
+    rows, cols = shape
+    for center, strength, radius in (((cols / 2, rows / 2), 0.3, 120.0), ((cols / 3, rows / 2 + 5.5), -0.8, 60.0),
+                                     ((cols / 2, rows / 2), 2.5, 200.0)):
+        ref = warps.swirl(img, center=np.array(center), strength=strength, radius=radius)
+        out = swirl_image(img, center, strength, radius)
+        assert out.shape == img.shape and out.dtype == np.float64
+        assert np.abs(out - ref).max() <= 1e-12
+        assert out.min() >= img.min() and out.max() <= img.max()
+    same = swirl_image(img, (cols / 2, rows / 2), 0.0, 100.0)
+    assert np.abs(same - img).max() <= 1e-15
+
+
+def test_add_swirl_standalone_matches_oracle():
+    """``add_swirl`` (mojave.py:222-261): first jet draws strength and radius, the second jet varies the
+    first one's by ~10 %; parameters equal, images within 1e-12."""
+    from oracle import mojave as om
+    from radiosim_b200 import mojave as m
+
+    size = 192
+    jet = om.base_jet(size, 2.0, 7.0, 40.0, 4.0)
+    r_o, r_g = np.random.default_rng(12), np.random.default_rng(12)
+    ref1, p_o = om.swirl_jet(jet, r_o)
+    out1, p_g = m.add_swirl(jet, r_g)
+    assert p_o[0] == p_g[0] and p_o[1] == p_g[1] and np.array_equal(p_o[2], p_g[2])
+    assert np.abs(out1 - ref1).max() <= 1e-12
+    ref2, q_o = om.swirl_jet(jet[:, ::-1].copy(), r_o, first=p_o)
+    out2, q_g = m.add_swirl(jet[:, ::-1].copy(), r_g, first_jet_params=p_g)
+    assert q_o[0] == q_g[0] and q_o[1] == q_g[1]
+    assert np.abs(out2 - ref2).max() <= 1e-12
+    assert r_o.random() == r_g.random()
