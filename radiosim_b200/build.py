@@ -19,7 +19,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC,-O2,-Wall",
+    "-Xcompiler", "-fPIC,-O3,-Wall",
     "--ptxas-options=-v", *os.environ.get("RSB_NVCC_EXTRA", "").split(),
 ]
 

@@ -20,6 +20,8 @@
 #include <cstdint>
 #include <cstring>
 #include <new>
+#include <thread>
+#include <vector>
 
 #include "common.cuh"
 
@@ -474,6 +476,31 @@ extern "C" int rsb_survey_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_g
 // `count` draws of RandomState.normal() (loc 0, scale 1: the value is legacy_gauss itself) as
 // float32 -- the noise fields of add_noise, reference src/radiosim/utils/utils.py:277,291
 // (np.random.normal(size=img_shape)), drawn in stream order.  Same state hand-over as rsb_jet_pack.
+// The stream itself is sequential, but only its cheap half is: the calling thread runs the generator and
+// the polar method's rejection test (accepted pairs x1, x2, r2), worker threads turn blocks of accepted
+// pairs into sqrt(-2 log(r2) / r2) * {x2, x1} -- the same double operations in the same order per value,
+// so the output is bit-identical to one legacy_gauss() call after the other.
+namespace rsb {
+namespace pack {
+struct PairBlock {
+  std::vector<double> x1, x2, r2;
+  std::vector<std::thread> workers;
+  void join() {
+    for (auto& t : workers) t.join();
+    workers.clear();
+  }
+};
+inline int fill_threads() {
+  if (const char* e = getenv("RSB_HOST_THREADS")) {
+    const int v = atoi(e);
+    if (v >= 1) return v > 64 ? 64 : v;
+  }
+  const unsigned hw = std::thread::hardware_concurrency();
+  return hw >= 16 ? 8 : (hw >= 4 ? (int)hw / 2 : 1);
+}
+}  // namespace pack
+}  // namespace rsb
+
 extern "C" int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_gauss,
                                       double* cached_gauss, long long count, float* out) {
   using namespace rsb::pack;
@@ -481,7 +508,80 @@ extern "C" int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t
           "rsb_legacy_normal_fill: NULL argument");
   RSB_ARG(count >= 0 && *mt_pos >= 0 && *mt_pos <= 624, "rsb_legacy_normal_fill: bad count / generator position");
   Legacy g{mt_key, *mt_pos, *has_gauss, *cached_gauss};
-  for (long long i = 0; i < count; ++i) out[i] = (float)g.legacy_gauss();
+  long long i = 0;
+  if (count > 0 && g.has_gauss) out[i++] = (float)g.legacy_gauss();  // the value a previous call left behind
+  const long long pairs = (count - i) / 2;
+  const int threads = fill_threads();
+  if (pairs < 32768 || threads <= 1) {
+    for (; i < count; ++i) out[i] = (float)g.legacy_gauss();
+  } else {
+    constexpr long long kBlock = 1 << 18;  // pairs per block (6 MB of doubles)
+    PairBlock blocks[2];
+    int which = 0;
+    try {
+      for (long long p0 = 0; p0 < pairs; p0 += kBlock, which ^= 1) {
+        PairBlock& b = blocks[which];
+        b.join();  // the block filled two rounds ago has been consumed
+        const long long np = (pairs - p0) < kBlock ? (pairs - p0) : kBlock;
+        b.x1.resize(np); b.x2.resize(np); b.r2.resize(np);
+        // legacy_gauss's rejection loop, values kept for the workers.  The generator's words are tempered
+        // a whole state array at a time (plain loops the compiler vectorises) and consumed from there.
+        double* X1 = b.x1.data();
+        double* X2 = b.x2.data();
+        double* R2 = b.r2.data();
+        for (long long p = 0; p < np;) {
+          if (g.pos == 624) g.refill();
+          uint32_t w[624];
+          const int avail = 624 - g.pos;
+          for (int q = 0; q < avail; ++q) {
+            uint32_t y = g.key[g.pos + q];
+            y ^= (y >> 11);
+            y ^= (y << 7) & 0x9d2c5680u;
+            y ^= (y << 15) & 0xefc60000u;
+            y ^= (y >> 18);
+            w[q] = y;
+          }
+          int q = 0;
+          for (; q + 4 <= avail && p < np; q += 4) {  // one candidate pair = four words
+            const double s1 = ((double)(int32_t)(w[q] >> 5) * 67108864.0 + (double)(int32_t)(w[q + 1] >> 6)) / 9007199254740992.0;
+            const double s2 = ((double)(int32_t)(w[q + 2] >> 5) * 67108864.0 + (double)(int32_t)(w[q + 3] >> 6)) / 9007199254740992.0;
+            const double x1 = 2.0 * s1 - 1.0, x2 = 2.0 * s2 - 1.0, r2 = x1 * x1 + x2 * x2;
+            X1[p] = x1; X2[p] = x2; R2[p] = r2;
+            p += (r2 >= 1.0 || r2 == 0.0) ? 0 : 1;   // rejected: overwritten by the next candidate
+          }
+          g.pos += q;
+          if (p < np && g.pos < 624) {  // fewer than four words left in the array: one pair across the refill
+            double x1, x2, r2;
+            x1 = 2.0 * g.sample() - 1.0;
+            x2 = 2.0 * g.sample() - 1.0;
+            r2 = x1 * x1 + x2 * x2;
+            if (!(r2 >= 1.0 || r2 == 0.0)) { X1[p] = x1; X2[p] = x2; R2[p] = r2; ++p; }
+          }
+        }
+        float* dst = out + i + 2 * p0;
+        const long long per = (np + threads - 1) / threads;
+        for (int t = 0; t < threads; ++t) {
+          const long long a = t * per, e = (a + per) < np ? (a + per) : np;
+          if (a >= e) break;
+          b.workers.emplace_back([&b, dst, a, e] {
+            for (long long p = a; p < e; ++p) {
+              const double r2 = b.r2[p];
+              const double f = std::sqrt(-2.0 * std::log(r2) / r2);
+              dst[2 * p] = (float)(f * b.x2[p]);      // returned first
+              dst[2 * p + 1] = (float)(f * b.x1[p]);  // the cached second variate
+            }
+          });
+        }
+      }
+    } catch (...) {
+      blocks[0].join(); blocks[1].join();
+      rsb::set_error("rsb_legacy_normal_fill: out of host memory or threads");
+      return 1;
+    }
+    blocks[0].join(); blocks[1].join();
+    i += 2 * pairs;
+    for (; i < count; ++i) out[i] = (float)g.legacy_gauss();  // an odd count leaves its second variate cached
+  }
   *mt_pos = g.pos;
   *has_gauss = g.has_gauss;
   *cached_gauss = g.gauss;

@@ -137,3 +137,31 @@ def test_native_ppdisk_packer_matches_python():
             assert np.array_equal(comps[f], rc[f]), f
         assert np.allclose(comps["scale"], rc["scale"], rtol=2e-7, atol=0)
     assert pp.pack_protos_native(3, 128, (0.5, 180), (3, 15), (0.1, 1)) is None
+
+
+@pytest.mark.parametrize("threads", ["1", "3", "8"])
+def test_legacy_normal_fill_equals_numpy(threads, monkeypatch):
+    """``rsb_legacy_normal_fill`` (add_noise's ``np.random.normal(size=...)``, utils.py:277,291): the
+    generator and the polar method's rejection run on the calling thread, the log / sqrt on workers --
+    values (as float32), cached second variate and stream position equal numpy's for even and odd
+    counts, with and without a cached variate at entry, across block boundaries."""
+    import ctypes as C
+
+    from radiosim_b200 import _lib as L
+
+    monkeypatch.setenv("RSB_HOST_THREADS", threads)
+    for count, pre in ((0, 0), (1, 1), (5, 0), (65537, 1), (2 * (1 << 18) + 70001, 0), (3 * (1 << 18) * 2 + 7, 3)):
+        np.random.seed(7)
+        for _ in range(pre):
+            np.random.normal()
+        name, key, pos, hg, cg = np.random.get_state()
+        key = np.ascontiguousarray(key, dtype=np.uint32).copy()
+        c_pos, c_has, c_c = C.c_int32(int(pos)), C.c_int32(int(hg)), C.c_double(float(cg))
+        out = np.empty(max(count, 1), np.float32)
+        L.check(L.lib().rsb_legacy_normal_fill(key.ctypes.data, C.byref(c_pos), C.byref(c_has), C.byref(c_c),
+                                               count, out.ctypes.data), "rsb_legacy_normal_fill")
+        ref = np.random.normal(size=count).astype(np.float32)
+        after = np.random.get_state()
+        assert np.array_equal(out[:count], ref), (count, pre)
+        assert c_pos.value == after[2] and c_has.value == after[3] and c_c.value == after[4]
+        assert np.array_equal(key, after[1])
