@@ -71,7 +71,7 @@ def test_create_proto_corner_grid_matches_oracle():
     from radiosim_b200.ppdisks import create_proto
 
     k = 0
-    for img_size in (128, 256):
+    for img_size in (128, 256, 512):
         for alpha in (0.0, 180.0):
             for ratio in (3, 15):
                 for size_ratio in (0.1, 1.0):
@@ -79,3 +79,21 @@ def test_create_proto_corner_grid_matches_oracle():
                     o = opp.create_proto(img_size, alpha, ratio, size_ratio, seed=100 + k)
                     g = np.asarray(create_proto(img_size, alpha, ratio, size_ratio, seed=100 + k))
                     assert np.allclose(o, g, rtol=1e-5, atol=1e-8), (img_size, alpha, ratio, size_ratio)
+
+
+def test_create_proto_no_seed_runs_like_the_reference_test():
+    """tests/test_ppdisks_simulation.py:37-55 as the reference runs it (``seed=None``: the global stream
+    is used as it stands): every corner renders, finite, non-negative, on the 1e-10 background."""
+    from radiosim_b200.ppdisks import create_proto
+
+    np.random.seed(99)
+    for img_size in (128, 512):
+        for alpha in (0.0, 180.0):
+            for ratio in (3, 15):
+                for size_ratio in (0.1, 1.0):
+                    before = np.random.get_state()[2]
+                    g = np.asarray(create_proto(img_size=img_size, alpha=alpha, ratio=ratio, size_ratio=size_ratio,
+                                                seed=None))
+                    assert g.shape == (img_size, img_size) and g.dtype == np.float32
+                    assert np.isfinite(g).all() and g.min() >= 1e-10 * (1 - 1e-6) and g.max() > 1e-10
+                    assert np.random.get_state()[2] != before       # (draws came from the global stream)
