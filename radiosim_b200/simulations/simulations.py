@@ -96,9 +96,13 @@ def create_sky_distribution(conf, bundles, mode, opt, rng=None, rank=0, world=1)
     out.mkdir(parents=True, exist_ok=True)
     written = []
     sky = target = data = None
-    writer = _ShardWriter()
     bundles = list(bundles)
     b = conf.dataset.bundle_size
+    # small shards (the default TOML: 2.6 MB each) are bound by per-file latency, not by bandwidth: more
+    # writer threads; large ones keep three, so that at most three bundles' page-locked blocks are held
+    shard_bytes = b * conf.dataset.img_size**2 * 8 * 2
+    lanes = int(max(3, min(8, (64 << 20) // max(shard_bytes, 1))))
+    writer = _ShardWriter(workers=lanes, depth=lanes)
     try:
         pos = 0
         while pos < len(bundles):
