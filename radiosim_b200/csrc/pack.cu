@@ -16,6 +16,7 @@
 // Elementary functions are libm's; numpy's array loops may use SIMD variants that differ in the
 // last bit, so parameters agree with the Python packer to ~1 ulp (tests/test_packer.py), the
 // stream position and every branch exactly.
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -476,20 +477,15 @@ extern "C" int rsb_survey_pack(uint32_t* mt_key, int32_t* mt_pos, int32_t* has_g
 // `count` draws of RandomState.normal() (loc 0, scale 1: the value is legacy_gauss itself) as
 // float32 -- the noise fields of add_noise, reference src/radiosim/utils/utils.py:277,291
 // (np.random.normal(size=img_shape)), drawn in stream order.  Same state hand-over as rsb_jet_pack.
-// The stream itself is sequential, but only its cheap half is: the calling thread runs the generator and
-// the polar method's rejection test (accepted pairs x1, x2, r2), worker threads turn blocks of accepted
-// pairs into sqrt(-2 log(r2) / r2) * {x2, x1} -- the same double operations in the same order per value,
-// so the output is bit-identical to one legacy_gauss() call after the other.
+// The stream itself is sequential, but only its cheapest part is: the calling thread runs MT19937 and
+// tempers its words, a block of candidate pairs at a time (four words per candidate, accepted or not, so
+// candidate k of a block sits at a known place); worker threads then do everything else -- the polar
+// method's rejection test, sqrt(-2 log(r2) / r2) * {x2, x1} for the accepted pairs -- on their share of the
+// candidates and write the results where a prefix sum of the accepted counts puts them.  Every value goes
+// through the same double operations in the same order as in legacy_gauss(), so the output, the cached
+// second variate and the stream position equal one call after the other.
 namespace rsb {
 namespace pack {
-struct PairBlock {
-  std::vector<double> x1, x2, r2;
-  std::vector<std::thread> workers;
-  void join() {
-    for (auto& t : workers) t.join();
-    workers.clear();
-  }
-};
 inline int fill_threads() {
   if (const char* e = getenv("RSB_HOST_THREADS")) {
     const int v = atoi(e);
@@ -497,6 +493,33 @@ inline int fill_threads() {
   }
   const unsigned hw = std::thread::hardware_concurrency();
   return hw >= 16 ? 8 : (hw >= 4 ? (int)hw / 2 : 1);
+}
+// n tempered words of the stream into w (the generator ends up behind them)
+inline void gen_words(Legacy& g, uint32_t* w, long long n) {
+  while (n > 0) {
+    if (g.pos == 624) g.refill();
+    const int step = (int)((624 - g.pos) < n ? (624 - g.pos) : n);
+    const uint32_t* k = g.key + g.pos;
+    for (int q = 0; q < step; ++q) {
+      uint32_t y = k[q];
+      y ^= (y >> 11);
+      y ^= (y << 7) & 0x9d2c5680u;
+      y ^= (y << 15) & 0xefc60000u;
+      y ^= (y >> 18);
+      w[q] = y;
+    }
+    g.pos += step;
+    w += step;
+    n -= step;
+  }
+}
+inline void skip_words(Legacy& g, long long n) {
+  while (n > 0) {
+    if (g.pos == 624) g.refill();
+    const int step = (int)((624 - g.pos) < n ? (624 - g.pos) : n);
+    g.pos += step;
+    n -= step;
+  }
 }
 }  // namespace pack
 }  // namespace rsb
@@ -512,76 +535,94 @@ extern "C" int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t
   if (count > 0 && g.has_gauss) out[i++] = (float)g.legacy_gauss();  // the value a previous call left behind
   const long long pairs = (count - i) / 2;
   const int threads = fill_threads();
-  if (pairs < 32768 || threads <= 1) {
-    for (; i < count; ++i) out[i] = (float)g.legacy_gauss();
-  } else {
-    constexpr long long kBlock = 1 << 18;  // pairs per block (6 MB of doubles)
-    PairBlock blocks[2];
-    int which = 0;
+  constexpr long long kSmall = 32768;  // pairs below which threads do not pay
+  if (pairs >= kSmall && threads > 1) {
+    constexpr long long kCand = 1 << 19;  // candidates per block (8 MB of words)
     try {
-      for (long long p0 = 0; p0 < pairs; p0 += kBlock, which ^= 1) {
-        PairBlock& b = blocks[which];
-        b.join();  // the block filled two rounds ago has been consumed
-        const long long np = (pairs - p0) < kBlock ? (pairs - p0) : kBlock;
-        b.x1.resize(np); b.x2.resize(np); b.r2.resize(np);
-        // legacy_gauss's rejection loop, values kept for the workers.  The generator's words are tempered
-        // a whole state array at a time (plain loops the compiler vectorises) and consumed from there.
-        double* X1 = b.x1.data();
-        double* X2 = b.x2.data();
-        double* R2 = b.r2.data();
-        for (long long p = 0; p < np;) {
-          if (g.pos == 624) g.refill();
-          uint32_t w[624];
-          const int avail = 624 - g.pos;
-          for (int q = 0; q < avail; ++q) {
-            uint32_t y = g.key[g.pos + q];
-            y ^= (y >> 11);
-            y ^= (y << 7) & 0x9d2c5680u;
-            y ^= (y << 15) & 0xefc60000u;
-            y ^= (y >> 18);
-            w[q] = y;
-          }
-          int q = 0;
-          for (; q + 4 <= avail && p < np; q += 4) {  // one candidate pair = four words
-            const double s1 = ((double)(int32_t)(w[q] >> 5) * 67108864.0 + (double)(int32_t)(w[q + 1] >> 6)) / 9007199254740992.0;
-            const double s2 = ((double)(int32_t)(w[q + 2] >> 5) * 67108864.0 + (double)(int32_t)(w[q + 3] >> 6)) / 9007199254740992.0;
-            const double x1 = 2.0 * s1 - 1.0, x2 = 2.0 * s2 - 1.0, r2 = x1 * x1 + x2 * x2;
-            X1[p] = x1; X2[p] = x2; R2[p] = r2;
-            p += (r2 >= 1.0 || r2 == 0.0) ? 0 : 1;   // rejected: overwritten by the next candidate
-          }
-          g.pos += q;
-          if (p < np && g.pos < 624) {  // fewer than four words left in the array: one pair across the refill
-            double x1, x2, r2;
-            x1 = 2.0 * g.sample() - 1.0;
-            x2 = 2.0 * g.sample() - 1.0;
-            r2 = x1 * x1 + x2 * x2;
-            if (!(r2 >= 1.0 || r2 == 0.0)) { X1[p] = x1; X2[p] = x2; R2[p] = r2; ++p; }
-          }
+      // scratch kept between calls (add_noise fills three fields per bundle): ~22 MB at most
+      static thread_local std::vector<uint32_t> words;
+      static thread_local std::vector<double> X1, X2, R2;
+      static thread_local std::vector<int32_t> cidx;
+      {
+        long long cap = (long long)((double)pairs * 1.2732) + 64;
+        if (cap > kCand) cap = kCand;
+        if ((long long)X1.size() < cap) {
+          words.resize((size_t)4 * cap); X1.resize((size_t)cap); X2.resize((size_t)cap); R2.resize((size_t)cap);
+          cidx.resize((size_t)cap);
         }
-        float* dst = out + i + 2 * p0;
-        const long long per = (np + threads - 1) / threads;
+      }
+      std::vector<long long> cnt((size_t)threads);
+      long long done = 0;
+      while (pairs - done >= kSmall) {
+        const long long need = pairs - done;
+        // a little under the expected requirement (acceptance pi/4), so that the last block rarely overshoots
+        long long nc = (long long)((double)need * 1.2732 * 0.985);
+        if (nc > kCand) nc = kCand;
+        uint32_t snap[624];
+        std::memcpy(snap, g.key, sizeof(snap));
+        const int snap_pos = g.pos;
+        gen_words(g, words.data(), 4 * nc);
+        std::atomic<int> arrived{0};
+        const long long per = (nc + threads - 1) / threads;
+        float* dst = out + i + 2 * done;
+        std::vector<std::thread> pool;
+        // (plain pointers: a lambda that names a thread_local vector would see the WORKER's own, empty one)
+        uint32_t* const Wp = words.data();
+        double* const pX1 = X1.data();
+        double* const pX2 = X2.data();
+        double* const pR2 = R2.data();
+        int32_t* const pC = cidx.data();
         for (int t = 0; t < threads; ++t) {
-          const long long a = t * per, e = (a + per) < np ? (a + per) : np;
-          if (a >= e) break;
-          b.workers.emplace_back([&b, dst, a, e] {
-            for (long long p = a; p < e; ++p) {
-              const double r2 = b.r2[p];
+          pool.emplace_back([&, t] {
+            const long long a = t * per, e = (a + per) < nc ? (a + per) : nc;
+            long long k = 0;
+            for (long long c = a; c < e; ++c) {
+              const uint32_t* w = Wp + (size_t)4 * c;
+              const double s1 = ((double)(int32_t)(w[0] >> 5) * 67108864.0 + (double)(int32_t)(w[1] >> 6)) / 9007199254740992.0;
+              const double s2 = ((double)(int32_t)(w[2] >> 5) * 67108864.0 + (double)(int32_t)(w[3] >> 6)) / 9007199254740992.0;
+              const double x1 = 2.0 * s1 - 1.0, x2 = 2.0 * s2 - 1.0, r2 = x1 * x1 + x2 * x2;
+              pX1[a + k] = x1; pX2[a + k] = x2; pR2[a + k] = r2; pC[a + k] = (int32_t)c;
+              k += (r2 >= 1.0 || r2 == 0.0) ? 0 : 1;   // rejected: overwritten by the next candidate
+            }
+            cnt[t] = a < e ? k : 0;
+            arrived.fetch_add(1, std::memory_order_acq_rel);
+            while (arrived.load(std::memory_order_acquire) < threads) std::this_thread::yield();
+            long long off = 0;
+            for (int u = 0; u < t; ++u) off += cnt[u];
+            long long mine = cnt[t];
+            if (off + mine > need) mine = need > off ? need - off : 0;  // (the last block may overshoot)
+            for (long long q = 0; q < mine; ++q) {
+              const double r2 = pR2[a + q];
               const double f = std::sqrt(-2.0 * std::log(r2) / r2);
-              dst[2 * p] = (float)(f * b.x2[p]);      // returned first
-              dst[2 * p + 1] = (float)(f * b.x1[p]);  // the cached second variate
+              dst[2 * (off + q)] = (float)(f * pX2[a + q]);      // returned first
+              dst[2 * (off + q) + 1] = (float)(f * pX1[a + q]);  // the cached second variate
             }
           });
         }
+        for (auto& th : pool) th.join();
+        long long total = 0;
+        for (int t = 0; t < threads; ++t) total += cnt[t];
+        if (total > need) {
+          // overshoot: the stream must stop behind the candidate that gave the last pair needed
+          long long off = 0, last_cand = -1;
+          for (int t = 0; t < threads && last_cand < 0; ++t) {
+            if (off + cnt[t] >= need) last_cand = pC[(size_t)(t * per + (need - off - 1))];
+            off += cnt[t];
+          }
+          std::memcpy(g.key, snap, sizeof(snap));
+          g.pos = snap_pos;
+          skip_words(g, 4 * (last_cand + 1));
+          total = need;
+        }
+        done += total;
       }
+      i += 2 * done;
     } catch (...) {
-      blocks[0].join(); blocks[1].join();
       rsb::set_error("rsb_legacy_normal_fill: out of host memory or threads");
       return 1;
     }
-    blocks[0].join(); blocks[1].join();
-    i += 2 * pairs;
-    for (; i < count; ++i) out[i] = (float)g.legacy_gauss();  // an odd count leaves its second variate cached
   }
+  for (; i < count; ++i) out[i] = (float)g.legacy_gauss();  // the rest (and an odd count's cached variate)
   *mt_pos = g.pos;
   *has_gauss = g.has_gauss;
   *cached_gauss = g.gauss;
