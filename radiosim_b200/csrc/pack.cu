@@ -553,10 +553,12 @@ extern "C" int rsb_legacy_normal_fill(uint32_t* mt_key, int32_t* mt_pos, int32_t
       }
       std::vector<long long> cnt((size_t)threads);
       long long done = 0;
+      double under = 0.985;
+      if (const char* e = getenv("RSB_DEBUG_FILL_FACTOR")) under = atof(e);  // (tests: > 1 forces the overshoot path)
       while (pairs - done >= kSmall) {
         const long long need = pairs - done;
         // a little under the expected requirement (acceptance pi/4), so that the last block rarely overshoots
-        long long nc = (long long)((double)need * 1.2732 * 0.985);
+        long long nc = (long long)((double)need * 1.2732 * under);
         if (nc > kCand) nc = kCand;
         uint32_t snap[624];
         std::memcpy(snap, g.key, sizeof(snap));

@@ -139,8 +139,8 @@ def test_native_ppdisk_packer_matches_python():
     assert pp.pack_protos_native(3, 128, (0.5, 180), (3, 15), (0.1, 1)) is None
 
 
-@pytest.mark.parametrize("threads", ["1", "3", "8"])
-def test_legacy_normal_fill_equals_numpy(threads, monkeypatch):
+@pytest.mark.parametrize("threads,factor", [("1", None), ("3", None), ("8", None), ("4", "1.05"), ("8", "1.3")])
+def test_legacy_normal_fill_equals_numpy(threads, factor, monkeypatch):
     """``rsb_legacy_normal_fill`` (add_noise's ``np.random.normal(size=...)``, utils.py:277,291): the
     generator and the polar method's rejection run on the calling thread, the log / sqrt on workers --
     values (as float32), cached second variate and stream position equal numpy's for even and odd
@@ -150,6 +150,8 @@ def test_legacy_normal_fill_equals_numpy(threads, monkeypatch):
     from radiosim_b200 import _lib as L
 
     monkeypatch.setenv("RSB_HOST_THREADS", threads)
+    if factor is not None:      # blocks sized above the expected requirement: the last one overshoots and
+        monkeypatch.setenv("RSB_DEBUG_FILL_FACTOR", factor)   # the generator is rewound behind its last used candidate
     for count, pre in ((0, 0), (1, 1), (5, 0), (65537, 1), (2 * (1 << 18) + 70001, 0), (3 * (1 << 18) * 2 + 7, 3)):
         np.random.seed(7)
         for _ in range(pre):
