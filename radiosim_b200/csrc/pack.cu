@@ -491,7 +491,11 @@ inline int fill_threads() {
     const int v = atoi(e);
     if (v >= 1) return v > 64 ? 64 : v;
   }
-  const unsigned hw = std::thread::hardware_concurrency();
+  unsigned hw = std::thread::hardware_concurrency();
+  if (const char* e = getenv("LOCAL_WORLD_SIZE")) {  // one process per GPU (torchrun): the cores are shared
+    const int ranks = atoi(e);
+    if (ranks > 1) hw /= (unsigned)ranks;
+  }
   return hw >= 16 ? 8 : (hw >= 4 ? (int)hw / 2 : 1);
 }
 // n tempered words of the stream into w (the generator ends up behind them)
