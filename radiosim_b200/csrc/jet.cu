@@ -46,6 +46,8 @@ struct __align__(16) Fixed {
   int margin;
   unsigned long long best;
   float delta;
+  float2 blk[kMaxSlots];  // per live slot {2^(2C), 2^(6C)} of the four-row blocks, or {-1, -1}: one exp per pixel
+  float la[kMaxSlots];    // log2(amplitude) where the blocks are used
 };
 
 // 4 consecutive pixels of one row, all live components (culled per strip).
@@ -64,6 +66,50 @@ __device__ __forceinline__ void splat_row4(const Coef* __restrict__ coef, int nl
       const float d = dc + (float)j;
       const float t = fmaf(fmaf(c.A, d, Bq), d, Cq);
       acc[j] = fmaf(c.amp, ex2(t), acc[j]);
+    }
+  }
+}
+
+// One live slot over an 8-row x 64-column tile, two adjacent pixels per lane (packed FP32x2).  Rows in
+// blocks of four from two exponentials per column,
+//   E(i) = E0 U^i 2^(C (i^2 - i)),  E0 = g(r_b, c),  U = 2^(B dc + 2 C dr_b + C)
+// (half the MUFU work of one exponential per pixel; same scheme as jet2.cu), unless the slot does not
+// suit it (amplitude <= 0, sigma below ~0.6 px, non-finite): then one exponential per pixel.
+__device__ __forceinline__ void tile_slot(f2 acc2[8], const Coef& c, float la, float2 kk, float r0f, float c0f) {
+  const float d0 = (c0f - c.icf) - c.fc;
+  const f2 d = f2_pack(d0, d0 + 1.f);
+  const f2 Q = f2_mul(f2_pack(c.B, c.B), d);
+  const float dr0 = (r0f - c.irf) - c.fr;
+  if (kk.x > 0.f) {
+    const f2 Pq = f2_fma(f2_mul(f2_pack(c.A, c.A), d), d, f2_pack(la, la));  // A dc^2 + log2(amp)
+    const f2 k2 = f2_pack(kk.x, kk.x), k3 = f2_pack(kk.y, kk.y);
+#pragma unroll
+    for (int b = 0; b < 8; b += 4) {
+      const float dr = dr0 + (float)b;
+      const float Cq = c.C * dr * dr;
+      const float tw = fmaf(2.f * c.C, dr, c.C);  // 2 C dr + C
+      float ta, tb, wa, wb;
+      f2_unpack(f2_fma(f2_pack(dr, dr), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
+      f2_unpack(f2_add(Q, f2_pack(tw, tw)), wa, wb);
+      // (the clamp never binds where the block holds a pixel above the cut-off; elsewhere it keeps U^3 finite)
+      const f2 E0 = f2_pack(ex2(ta), ex2(tb));
+      const f2 U = f2_pack(ex2(fminf(wa, 40.f)), ex2(fminf(wb, 40.f)));
+      const f2 U2 = f2_mul(U, U);
+      acc2[b] = f2_add(acc2[b], E0);
+      acc2[b + 1] = f2_fma(E0, U, acc2[b + 1]);
+      acc2[b + 2] = f2_fma(E0, f2_mul(U2, k2), acc2[b + 2]);
+      acc2[b + 3] = f2_fma(E0, f2_mul(f2_mul(U2, U), k3), acc2[b + 3]);
+    }
+  } else {
+    const f2 Pq = f2_mul(f2_mul(f2_pack(c.A, c.A), d), d);
+    const f2 amp2 = f2_pack(c.amp, c.amp);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float dr = dr0 + (float)i;
+      const float Cq = c.C * dr * dr;
+      float ta, tb;
+      f2_unpack(f2_fma(f2_pack(dr, dr), Q, f2_add(Pq, f2_pack(Cq, Cq))), ta, tb);
+      acc2[i] = f2_fma(amp2, f2_pack(ex2(ta), ex2(tb)), acc2[i]);
     }
   }
 }
@@ -133,7 +179,27 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) jet_kernel(const Args a)
     const bool zoom = zpad >= 0;
     const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
 
-    if (warp == 0) build_coefs(sm, P, slots, N, lane);
+    if (warp == 0) {
+      build_coefs(sm, P, slots, N, lane);
+      __syncwarp();
+      bool nonneg = true;
+      float amax = 0.f;
+      for (int k = lane; k < slots; k += 32) {
+        nonneg = nonneg && !(P[k * 6] < 0.0);
+        amax = fmaxf(amax, fabsf((float)P[k * 6]));
+      }
+      nonneg = __all_sync(0xffffffffu, nonneg);
+      amax = warp_max(amax);
+      for (int k = lane; k < sm.nlive; k += 32) {
+        const Coef c = sm.coef[k];
+        const bool blocks = c.amp > 0.f && c.C >= -2.f && isfinite(c.A) && isfinite(c.B) && isfinite(c.C);
+        sm.la[k] = blocks ? log2f(c.amp) : 0.f;
+        sm.blk[k] = blocks ? make_float2(exp2f(2.f * c.C), exp2f(6.f * c.C)) : make_float2(-1.f, -1.f);
+      }
+      // float32 noise of a rendered pixel near the 0.01 threshold (see jet2.cu: relative to the pixel value
+      // when every amplitude is >= 0, plus the tails the footprint cut drops; else relative to the largest one)
+      if (lane == 0) sm.delta = nonneg ? 3e-7f + 4e-7f * amax : 6e-6f * fmaxf(1.f, amax);
+    }
     __syncthreads();
     const int nlive = sm.nlive;
     const float thr = (float)kEdgeThr, delta = sm.delta;
@@ -141,38 +207,53 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) jet_kernel(const Args a)
     // ---------------- phase 1: splat ------------------------------------------
     int my_margin = N;                  // zoom branch: min border distance of px > thr
     unsigned long long my_best = 0ull;  // else: (value bits << 32) | ~pixel index
-    for (int item = warp; item < items; item += kWarps) {
-      const int r = item / strips, s = item - r * strips;
-      const int c0 = s * kStrip + 4 * lane;
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      splat_row4(sm.coef, nlive, r, (float)r, s * kStrip, (float)c0, acc);
-      if (c0 < N) {
-        *reinterpret_cast<float4*>(raw + (size_t)r * pitch + c0) =
-            make_float4(acc[0], acc[1], acc[2], acc[3]);
-        if (zoom) {
-          const float top = fmaxf(fmaxf(acc[0], acc[1]), fmaxf(acc[2], acc[3]));
-          if (top > thr - delta) {
-            const int dr = min(r, N - 1 - r);
+    // 8 x 64 tiles, two adjacent pixels per lane; slots culled per tile by their > tau bounding box
+    const int tcols = (N + 63) >> 6, ntiles = ((N + 7) >> 3) * tcols;
+    for (int t = warp; t < ntiles; t += kWarps) {
+      const int g = t / tcols, tc0 = (t - g * tcols) << 6;
+      const int r0 = g << 3, c0 = tc0 + 2 * lane, rend = min(N, r0 + 8);
+      f2 acc2[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int c = c0 + j;
-              const int d = min(dr, min(c, N - 1 - c));
-              if (c < N && d < my_margin && acc[j] > thr - delta) {
-                bool above = acc[j] > thr;
-                if (acc[j] < thr + delta) above = eval64(P, slots, r, c) > kEdgeThr;
-                if (above) my_margin = d;
+      for (int i = 0; i < 8; ++i) acc2[i] = 0ull;
+      for (int k = 0; k < nlive; ++k) {
+        const Coef c = sm.coef[k];
+        if (rend - 1 < c.r0 || r0 > c.r1 || tc0 + 63 < c.c0 || tc0 > c.c1) continue;  // warp-uniform
+        tile_slot(acc2, c, sm.la[k], sm.blk[k], (float)r0, (float)c0);
+      }
+      if (c0 < N) {
+        const bool second = c0 + 1 < N;   // odd sizes: the pair's second column lies outside the image
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = r0 + i;
+          if (r >= rend) break;
+          float v[2];
+          f2_unpack(acc2[i], v[0], v[1]);
+          if (!second) v[1] = 0.f;
+          *reinterpret_cast<float2*>(raw + (size_t)r * pitch + c0) = make_float2(v[0], v[1]);
+          if (zoom) {
+            if (fmaxf(v[0], v[1]) > thr - delta) {
+              const int dr = min(r, N - 1 - r);
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                const int c = c0 + j;
+                const int d = min(dr, min(c, N - 1 - c));
+                if (c < N && d < my_margin && v[j] > thr - delta) {
+                  bool above = v[j] > thr;
+                  if (v[j] < thr + delta) above = eval64(P, slots, r, c) > kEdgeThr;
+                  if (above) my_margin = d;
+                }
               }
             }
-          }
-        } else if (normalize) {
+          } else if (normalize) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int c = c0 + j;
-            if (c < N) {
-              const unsigned long long key =
-                  ((unsigned long long)__float_as_uint(fmaxf(acc[j], 0.f)) << 32) |
-                  (unsigned)(~(unsigned)(r * N + c));
-              my_best = key > my_best ? key : my_best;
+            for (int j = 0; j < 2; ++j) {
+              const int c = c0 + j;
+              if (c < N) {
+                const unsigned long long key =
+                    ((unsigned long long)__float_as_uint(fmaxf(v[j], 0.f)) << 32) |
+                    (unsigned)(~(unsigned)(r * N + c));
+                my_best = key > my_best ? key : my_best;
+              }
             }
           }
         }
