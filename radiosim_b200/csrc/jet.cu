@@ -588,6 +588,20 @@ static int check_common(const char* fn, int n, int slots, int size) {
   return 0;
 }
 
+// sizes 257 .. 512 on the band renderer of jet3.cu (RSB_NO_BANDS=1: the scratch-image kernel below, for comparison)
+static bool bands_supported(int size, int slots, size_t* smem) {
+  static const bool off = [] { const char* e = getenv("RSB_NO_BANDS"); return e && e[0] == '1'; }();
+  return !off && v3_supported(size, slots, smem);
+}
+static int bands_launch(const double* params, const int32_t* zoom_pad, int n, int slots, int size, unsigned flags,
+                        void* out_img, int32_t* out_margin, double* out_peak, size_t smem, void* stream) {
+  Args a3;
+  a3.params = params; a3.zoom_pad = zoom_pad; a3.n = n; a3.slots = slots; a3.size = size;
+  a3.flags = flags; a3.out = out_img; a3.margin = out_margin; a3.peak = out_peak;
+  a3.scratch = nullptr; a3.pitch = (size + 3) & ~3;
+  return v3_launch(a3, smem, (cudaStream_t)stream);
+}
+
 extern "C" {
 
 int rsb_jet_workspace_bytes(int n, int slots, int size, size_t* bytes) {
@@ -596,7 +610,7 @@ int rsb_jet_workspace_bytes(int n, int slots, int size, size_t* bytes) {
   {
     int cluster = 1;
     size_t smem = 0;
-    if (v2_supported(size, slots, &cluster, &smem)) {
+    if (v2_supported(size, slots, &cluster, &smem) || bands_supported(size, slots, &smem)) {
       *bytes = 0;
       return 0;
     }
@@ -629,6 +643,8 @@ int rsb_jet_render(const double* params, const int32_t* zoom_pad, int n, int slo
       a2.scratch = nullptr; a2.pitch = (size + 3) & ~3;
       return v2_launch(a2, cluster, smem, (cudaStream_t)stream);
     }
+    if (bands_supported(size, slots, &smem))
+      return bands_launch(params, zoom_pad, n, slots, size, flags, out_img, out_margin, out_peak, smem, stream);
   }
   Plan p;
   if (int e = make_plan(size, &p)) return e;
@@ -843,6 +859,8 @@ int rsb_jet_render_static(const double* params, const int32_t* zoom_pad, int n, 
       a2.scratch = nullptr; a2.pitch = (size + 3) & ~3;
       return v2_launch(a2, cluster, smem, (cudaStream_t)stream);
     }
+    if (bands_supported(size, slots, &smem))
+      return bands_launch(params, zoom_pad, n, slots, size, flags, out_img, out_margin, out_peak, smem, stream);
   }
   Plan p;
   if (int e = make_plan(size, &p)) return e;

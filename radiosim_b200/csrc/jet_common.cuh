@@ -165,6 +165,9 @@ bool v2_supported(int size, int slots, int* cluster, size_t* smem_bytes);
 int v2_launch(const Args& a, int cluster, size_t smem_bytes, cudaStream_t st);
 // variable-size launch: a.size = largest size in the batch, a.sizes / a.out_offs per image
 int v2_launch_var(const Args& a, cudaStream_t st);
+// band renderer for 257 .. 512 pixels (jet3.cu): 8-CTA clusters, V pass through distributed shared memory
+bool v3_supported(int size, int slots, size_t* smem_bytes);
+int v3_launch(const Args& a, size_t smem_bytes, cudaStream_t st);
 
 }  // namespace jet
 }  // namespace rsb
