@@ -1,8 +1,9 @@
 // On-chip jet renderer for sizes 257 .. 512: the jet2.cu design with MORE THAN TWO row bands.
 // (reference: src/radiosim/jets/jet.py:144-192, utils/gauss.py:50-97, utils/utils.py:90-177)
 //
-// One image per thread-block cluster of 4 (size <= 384) or 8 CTAs; CTA k keeps rows [k Hb, (k+1) Hb) of the
-// raw image in its shared memory (Hb = rows per band, a multiple of 8).  Splat, margin search, tap table
+// One image per thread-block cluster of 8 CTAs; the image's 8-row groups are dealt round-robin, CTA k keeps
+// groups k, k + 8, ... in its shared memory (the jet sits around the centre: contiguous bands leave the outer
+// CTAs idle).  Splat, margin search, tap table
 // and the H pass are band-local exactly as in jet2.cu.  The composite zoom operator only preserves the image
 // centre, so with more than two bands an output row's taps can lie in ANOTHER CTA's band: the V pass reads
 // them through distributed shared memory (ld.shared::cluster), between two cluster barriers (every band's H
@@ -169,7 +170,7 @@ __device__ __forceinline__ int round_fma(float x) {
 
 #define RSB_BSTAMP(k) do {} while (0)
 __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
-                                    int H, int lane, bool zoom, int first_worker,
+                                    int H, int lane, bool zoom, int first_worker, int bands, int rank,
                                     long long* dbg_tl = nullptr) {
   RSB_BSTAMP(0);
   SlotGeo* geo = reinterpret_cast<SlotGeo*>(sm.geo);
@@ -319,8 +320,9 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
       if (u < ntiles) {
         const unsigned inv_tc = (65536u + (unsigned)tcols - 1u) / (unsigned)tcols;
         const int g = (int)(((unsigned)u * inv_tc) >> 16), tc = u - g * tcols;
-        const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols;
-        const int rend = min(R0 + H, r0 + kTileRows);
+        // (8-row groups are dealt round-robin to the CTAs of the cluster: local group g = absolute g * bands + rank)
+        const int r0 = (g * bands + rank) * kTileRows, tc0 = tc * kTileCols;
+        const int rend = min(N, r0 + kTileRows);
         // every pixel of the tile closer than dlo to the border: never read, never above 0.01
         // (two pixels of slack: zero-weight taps may touch the crop's neighbours)
         const int rmid = min(max(N >> 1, r0), rend - 1), cmid = min(max(N >> 1, tc0), min(tc0 + kTileCols, N) - 1);
@@ -772,20 +774,29 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
     npad = (N + 3) & ~3;
     pitch = a.pitch;
     opitch = N;
-    Hb = (N + kCluster - 1) / kCluster;           // every band non-empty: (kCluster - 1) Hb < N for N >= 50
-    R0 = keep_s32(rank * Hb);
-    H = min(Hb, N - R0);
-    base = R0;
+    // 8-row groups dealt round-robin: CTA k holds groups k, k + kCluster, ... (the jet sits around the image
+    // centre: contiguous bands would leave the outer CTAs idle).  Local row lr <-> absolute row
+    // ((lr >> 3) kCluster + k) 8 + (lr & 7).
+    {
+      const int G = (N + kTileRows - 1) / kTileRows;          // groups of the image
+      const int ngl = (G - rank + kCluster - 1) / kCluster;   // ... of this CTA (>= 1 for N >= 8 kCluster)
+      const int last = ((ngl - 1) * kCluster + rank) * kTileRows;
+      Hb = ((G + kCluster - 1) / kCluster) * kTileRows;       // rows allocated per CTA
+      H = (ngl - 1) * kTileRows + min(kTileRows, N - last);   // local rows in use
+    }
+    R0 = 0;      // (local row 0; absolute rows come from abs_row())
+    base = 0;
     strips = (N + kStrip - 1) / kStrip;           // 128-column strips (H/V pass)
     tcols = (N + kTileCols - 1) / kTileCols;      // 64-column tiles (phase 1)
     vec = (opitch & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
     // float32 output with contiguous rows: the first stage_rows rows of the finished band are staged in
     // shared memory and leave through one bulk async copy that drains while the next image is rendered
-    stage_rows = (!f64 && vec && pitch == N) ? min(a.stage_rows, H) : 0;
+    stage_rows = 0;  // (a CTA's rows are not contiguous in the output: no staged bulk store)
     stage = raw + (size_t)Hb * pitch;
     s_stage = keep_u32(smem_u32(stage));
   };
   geometry(a.size);
+  auto abs_row = [&](int lr) -> int { return (((lr >> 3) * kCluster + rank) << 3) + (lr & 7); };
   int xuse[3] = {0, 0, 0};  // uses so far of each exchange mbarrier (same in every CTA)
   // all-gather of one 64-bit value per CTA (all threads call; the value is CTA-uniform): thread 0 writes it
   // into slot [rank] of every peer with st.async, completion counted on the receiver's mbarrier; returns
@@ -845,7 +856,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
   if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
     if constexpr (kBig) build_coefs2_big<4>(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker);
-    else build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker);
+    else build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker, kCluster, rank);
   }
   // the peer CTA is resident and its mbarriers are initialised before any st.async
   if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -907,7 +918,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
                                 a.zoom_pad[img + nclusters] >= 0, first_worker);
           else
             build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane,
-                         a.zoom_pad[img + nclusters] >= 0, first_worker);
+                         a.zoom_pad[img + nclusters] >= 0, first_worker, kCluster, rank);
         }
         RSB_STAMP_T(12, kCoefWarp * 32);
       } else if (warp == kLabelWarp) {
@@ -955,9 +966,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       uint2 nx = make_uint2(0u, kRecEnd);
       if (e + 1 < kMaxRec) nx = lds_v2u(s_rec + (uint32_t)(e + 1) * 8u);
       const int g = (int)(rc.y >> 8), tc = (int)(rc.y & 0xffu);
-      const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
-      const uint32_t s_dst = s_raw + (uint32_t)((r0 - base) * pitch + c0) * 4u;
-      const int rend = min(R0 + H, r0 + kTileRows);  // rows of this tile that exist
+      const int r0 = (g * kCluster + rank) * kTileRows, tc0 = tc * kTileCols, c0 = tc0 + 2 * lane;
+      const uint32_t s_dst = s_raw + (uint32_t)(g * kTileRows * pitch + c0) * 4u;  // local rows g 8 ..
+      const int rend = min(N, r0 + kTileRows);  // rows of this tile that exist
       const float r0f = (float)r0, c0f = (float)c0;
       if (rc.x == 0u) {
         // no slot touches this tile: zeros (the resampling taps may still read them)
@@ -1254,25 +1265,13 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       RSB_STAMP(2);
       const float inv = normalize ? 1.f / __uint_as_float((unsigned)(image_best >> 32)) : 1.f;
       const int q4 = npad >> 2;
-      if (!f64 && vec && pitch == opitch) {
-        // float32, 16-byte aligned contiguous rows: the band is one run of float4
-        const uint32_t s_src = s_raw + (uint32_t)((R0 - base) * pitch) * 4u;
-        float4* outv = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + (size_t)R0 * opitch);
-        const int nstage = stage_rows * q4;
-        for (int e = tid; e < H * q4; e += kWorkers) {
-          float4 v = lds_v4(s_src + (uint32_t)e * 16u);
-          v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-          if (e < nstage) sts_v4(s_stage + (uint32_t)e * 16u, v);
-          else outv[e] = v;
-        }
-      } else {
-        for (int e = tid; e < H * q4; e += kWorkers) {
-          const int rl = e / q4, c0 = (e - rl * q4) << 2;
-          const int r = R0 + rl;
-          float4 v = lds_v4(s_raw + (uint32_t)((r - base) * pitch + c0) * 4u);
-          v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-          store_out4(out + (size_t)r * opitch * esz, f64, c0, N, vec, v);
-        }
+      for (int e = tid; e < H * q4; e += kWorkers) {
+        const int rl = e / q4, c0 = (e - rl * q4) << 2;
+        const int r = abs_row(rl);
+        float4 v = lds_v4(s_raw + (uint32_t)(rl * pitch + c0) * 4u);
+        v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+        if (!f64 && vec) *reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + (size_t)r * opitch + c0) = v;
+        else store_out4(out + (size_t)r * opitch * esz, f64, c0, N, vec, v);
       }
     } else {
       // ------------- zoom branch ------------------------------------------------------
@@ -1349,22 +1348,39 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
           const int sc0 = s * kStrip;
           act[s] = (s < strips) && sc0 <= fhi && sc0 + kStrip - 1 >= flo;
         }
-        const int rlo = max(R0, margin), rhi = min(R0 + H, N - margin);
-        for (int r = rlo + warp; r < rhi; r += kWarps) {
-          const uint32_t s_row = s_raw + (uint32_t)((r - base) * pitch) * 4u;
+        for (int lr = warp; lr < H; lr += kWarps) {
+          const int r = abs_row(lr);
+          if (r < margin || r >= N - margin) continue;  // (warp-uniform) only the crop's rows are resampled
+          const uint32_t s_row = s_raw + (uint32_t)(lr * pitch) * 4u;
           float res[NS][4];
+          // two strips at a time: their eight tap records first, then the 24 gathers, then the arithmetic --
+          // independent loads in flight instead of sixteen dependent record -> gather -> fma chains
 #pragma unroll
-          for (int s = 0; s < NS; ++s) {
+          for (int s0 = 0; s0 < NS; s0 += 2) {
+            float4 tp[2][4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int cj = s * kStrip + 32 * j + lane;
-              res[s][j] = 0.f;
-              if (act[s]) {  // (warp-uniform)
-                const float4 tp = lds_v4(s_tab + (uint32_t)min(cj, npad - 1) * 16u);
-                const uint32_t src = s_row + (uint32_t)__float_as_int(tp.w) * 4u;
-                res[s][j] = fmaf(tp.z, lds_f32(src + 8u), fmaf(tp.y, lds_f32(src + 4u), tp.x * lds_f32(src)));
+            for (int q = 0; q < 2; ++q)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int cj = (s0 + q) * kStrip + 32 * j + lane;
+                tp[q][j] = (s0 + q < NS) ? lds_v4(s_tab + (uint32_t)min(cj, npad - 1) * 16u) : make_float4(0.f, 0.f, 0.f, 0.f);
               }
-            }
+            float v[2][4][3];
+#pragma unroll
+            for (int q = 0; q < 2; ++q)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const uint32_t src = s_row + (uint32_t)__float_as_int(tp[q][j].w) * 4u;
+                v[q][j][0] = lds_f32(src);
+                v[q][j][1] = lds_f32(src + 4u);
+                v[q][j][2] = lds_f32(src + 8u);
+              }
+#pragma unroll
+            for (int q = 0; q < 2; ++q)
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (s0 + q < NS)
+                  res[s0 + q][j] = fmaf(tp[q][j].z, v[q][j][2], fmaf(tp[q][j].y, v[q][j][1], tp[q][j].x * v[q][j][0]));
           }
           __syncwarp();
 #pragma unroll
@@ -1384,14 +1400,14 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       cg::this_cluster().sync();  // every band's T is complete: the V pass may read any CTA's rows
 
       RSB_STAMP(6);
-      const int vr0 = max(R0, flo), vr1 = min(R0 + H - 1, fhi);  // inclusive footprint rows
+      const int vr0 = flo, vr1 = fhi;  // inclusive footprint rows
       // absolute rows that hold T: the crop [margin, N - margin) -- in whichever CTA's band they lie
       const int tlo = margin, thi = max(N - margin - 1, margin);
       const uint32_t raw_off = s_raw;  // same offset in every CTA's shared window
       // address of T[row][c0 ..] in the shared memory of the CTA that owns the row
       auto t_row = [&](int row) -> uint32_t {
-        const int owner = row / Hb;
-        return cluster_map(raw_off + (uint32_t)((row - owner * Hb) * pitch) * 4u, (uint32_t)owner);
+        const int g = row >> 3, owner = g % kCluster, lr = ((g / kCluster) << 3) + (row & 7);
+        return cluster_map(raw_off + (uint32_t)(lr * pitch) * 4u, (uint32_t)owner);
       };
       if constexpr (kBig) {
         // V pass twice: the maximum first, then the same values again, scaled and stored
@@ -1459,10 +1475,10 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       best_i = 0;
 #pragma unroll
       for (int i = 0; i < kRowsPerWarp; ++i) {
-        const int r = R0 + warp + i * kWarps;
+        const int lr = warp + i * kWarps, r = abs_row(lr);
 #pragma unroll
         for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < vr0 || r > vr1) continue;  // warp-uniform
+        if (lr >= H || r < vr0 || r > vr1) continue;  // warp-uniform
         const float4 tp = lds_v4(s_tab + (uint32_t)r * 16u);
         const float w0 = tp.x, w1 = tp.y, w2 = tp.z;
         // only zero-weight taps can fall outside the crop: clamp them onto rows that hold T (0 x whatever an
@@ -1516,34 +1532,27 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       }
       RSB_STAMP(8);
       if (!f64 && vec) {
-        // float32, 16-byte aligned rows: the common case, kept free of the general store's
-        // branches (they cost more issue slots than the stores themselves)
-        // (running addresses, laundered: the compiler otherwise rebuilds the 64-bit address
-        // from the kernel arguments in front of every store)
-        float* outf = keep_ptr(reinterpret_cast<float*>(out) + (size_t)(R0 + warp) * opitch + 4 * lane);
-        uint32_t s_st = keep_u32(s_stage + (uint32_t)(warp * opitch + 4 * lane) * 4u);
-        const uint32_t step = keep_u32((uint32_t)(kWarps * opitch));  // floats between this warp's rows
+        // float32, 16-byte aligned rows: the common case, kept free of the general store's branches
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
           const int rl = warp + i * kWarps;
           if (rl < H) {
+            float* outf = reinterpret_cast<float*>(out) + (size_t)abs_row(rl) * opitch + 4 * lane;
 #pragma unroll
             for (int s = 0; s < NS; ++s) {
               if (s >= strips || s * kStrip + 4 * lane >= N) continue;
               float4 v = res[i][s];
               v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-              if (rl < stage_rows) sts_v4(s_st + (uint32_t)(s * kStrip) * 4u, v);
-              else *reinterpret_cast<float4*>(outf + s * kStrip) = v;
+              *reinterpret_cast<float4*>(outf + s * kStrip) = v;
             }
           }
-          outf += step;
-          s_st += step * 4u;
         }
       } else {
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
-          const int rl = warp + i * kWarps, r = R0 + rl;
+          const int rl = warp + i * kWarps;
           if (rl >= H) continue;
+          const int r = abs_row(rl);
 #pragma unroll
           for (int s = 0; s < NS; ++s) {
             const int c0 = s * kStrip + 4 * lane;
@@ -1612,20 +1621,22 @@ static int launch_v3(const Args& a, size_t smem_bytes, cudaStream_t st) {
 constexpr int kV3Cluster = 8;
 static size_t v3_bytes(int size, int stage_rows) {
   const int npad = (size + 3) & ~3;
-  const int rows = (size + kV3Cluster - 1) / kV3Cluster;
+  const int groups = (size + 7) / 8;
+  const int rows = ((groups + kV3Cluster - 1) / kV3Cluster) * 8;  // 8-row groups dealt round-robin
   return sizeof(v3::Fixed2) + (size_t)npad * 16 + (size_t)(rows + stage_rows) * npad * 4;
 }
 
-// sizes 257 .. 512 (8 bands of at most 64 rows), at most 32 slots
+// sizes 401 .. 512 (at most 64 rows per CTA), at most 32 slots.  Below ~400 pixels the scratch-image kernel of
+// jet.cu is faster (measured crossover: 384^2 1.01 vs 1.06 M images/s, 448^2 0.80 vs 0.70): the per-image cost of
+// eight CTAs' barriers and of the V pass's distributed-shared-memory reads does not shrink with the image.
 bool v3_supported(int size, int slots, size_t* smem_bytes) {
   int dev = 0, max_optin = 0;
-  if (slots > 32 || size <= 2 * 128 || size > kV3Cluster * v3::kMaxBand) return false;
+  if (slots > 32 || size <= 400 || size > kV3Cluster * v3::kMaxBand) return false;
   if (cudaGetDevice(&dev) != cudaSuccess) return false;
   if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess)
     return false;
   if (v3_bytes(size, 0) > (size_t)max_optin) return false;
-  const int half = ((size + kV3Cluster - 1) / kV3Cluster) / 2;
-  *smem_bytes = v3_bytes(size, v3_bytes(size, half) <= (size_t)max_optin ? half : 0);
+  *smem_bytes = v3_bytes(size, 0);  // (no staged bulk store: a CTA's rows are scattered over the image)
   return true;
 }
 

@@ -49,7 +49,11 @@ def test_create_jet_matches_reference_golden(golden_dir, name):
     (128, 40, 21, True), (64, 30, 22, False), (101, 12, 23, True), (150, 12, 24, False),
     (256, 24, 25, False), (300, 6, 26, True), (66, 10, 27, True),
     # odd sizes above 128: two CTAs per image with uneven bands (ceil / floor of N/2 rows)
-    (151, 12, 28, False), (199, 10, 29, True), (255, 8, 30, False), (130, 8, 31, False)])
+    (151, 12, 28, False), (199, 10, 29, True), (255, 8, 30, False), (130, 8, 31, False),
+    # 401 .. 512: eight CTAs per image, 8-row groups dealt round-robin, V pass through distributed shared
+    # memory (jet3.cu); 384: the scratch-image kernel; odd / not a multiple of 4 / of 8 among them
+    (512, 12, 32, False), (512, 6, 33, True), (404, 8, 34, False), (449, 8, 35, True), (470, 6, 36, False),
+    (401, 6, 37, False), (384, 6, 38, False)])
 def test_render_matches_oracle(size, n, seed, f64):
     """Same seed -> same parameters -> images within 1e-5 of peak, margins exact."""
     from oracle import jet as ojet

@@ -44,6 +44,9 @@ CASES = [
     (256, 19, "faint", True), (250, 19, "plain", True), (250, 9, "narrow", False), (130, 19, "negative", False),
     (128, 19, "narrow", True), (100, 7, "plain", True), (36, 5, "plain", True), (65, 5, "plain", True),
     (254, 19, "outside", True), (200, 32, "sparse", True),
+    # the band renderer for 401 .. 512 pixels (jet3.cu) and, at 33 slots / 384 pixels, the scratch-image kernel
+    (512, 19, "negative", True), (512, 19, "narrow", False), (480, 32, "outside", True), (430, 12, "wide", True),
+    (512, 19, "faint", True), (418, 19, "sparse", False), (512, 33, "plain", True), (384, 19, "narrow", True),
 ]
 
 

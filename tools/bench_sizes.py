@@ -7,7 +7,9 @@ from radiosim_b200.jets.packer import pack_jets
 lib = L.lib()
 CASES = ((64, 32768), (100, 16384), (128, 16384), (150, 8192), (200, 8192), (256, 8192), (384, 4096), (512, 2048), (1024, 512))
 want = [int(a) for a in sys.argv[1:]]
-for size, n in [c for c in CASES if not want or c[0] in want]:
+known = dict(CASES)
+cases = [(w, known.get(w, max(256, (1 << 29) // (w * w) // 256 * 256))) for w in want] if want else list(CASES)
+for size, n in cases:
     np.random.seed(1)
     b = pack_jets(n, size, (3, 10), "normalize")
     d_p, d_z = L.dev_from(b.params), L.dev_from(b.zoom_pad)
