@@ -43,7 +43,6 @@ constexpr int kThreads = kWorkers;
 constexpr int kTileRows = 8;
 constexpr int kTileCols = 64;   // 2 columns per lane
 constexpr int kMaxBand = 64;    // rows per CTA band (V-pass results live in registers: 4 rows per warp x 4 strips)
-constexpr int kBigMax = 224;    // largest image one CTA holds whole (V pass twice; 4 x 32 tiles of 8 x 64)
 constexpr int kRowsPerWarp = kMaxBand / kWarps;
 constexpr int kMaxGroups = kMaxBand / kTileRows;
 constexpr int kMaxCand = 64;
@@ -388,232 +387,6 @@ __device__ inline void build_coefs2(Fixed2& sm, int cb, const double* P, int slo
   RSB_BSTAMP(4);
 }
 
-// TPL = tiles per lane the work-list part can hold: 2 (bands of up to 128 rows x 256 columns) or 4 (one CTA
-// with the whole image, up to 224 rows)
-template <int TPL>
-__device__ inline void build_coefs2_big(Fixed2& sm, int cb, const double* P, int slots, int N, int R0,
-                                    int H, int lane, bool zoom, int first_worker,
-                                    long long* dbg_tl = nullptr) {
-  RSB_BSTAMP(0);
-  SlotGeo* geo = reinterpret_cast<SlotGeo*>(sm.geo);
-  float amax = 0.f;
-  for (int k = lane; k < slots; k += 32) amax = fmaxf(amax, fabsf((float)P[k * 6]));
-  amax = warp_max(amax);
-  const float tau = 2e-8f * amax;  // <= 19 x 2e-8 of the peak is dropped in total
-  const int ngroups = (H + kTileRows - 1) / kTileRows;
-  const int tcols = (N + kTileCols - 1) / kTileCols, ntiles = ngroups * tcols;
-  sm.hist[lane] = 0;
-  int base = 0;
-  bool certified = false, all_nonneg = true;
-  for (int k0 = 0; k0 < slots; k0 += 32) {
-    const int k = k0 + lane;
-    bool live = false;
-    Coef2 c;
-    SlotGeo g;
-    g.degenerate = 0;
-    if (k < slots) {
-      const double* p = P + k * 6;
-      const double xd = p[1], yd = p[2];
-      const float amp = (float)p[0], sx = (float)p[3], sy = (float)p[4];
-      if (p[0] != 0.0 && fabsf(amp) > tau) {
-        float sr, cr;
-        sincosf((float)p[5], &sr, &cr);
-        const float iu = 1.f / (sy * sy), iv = 1.f / (sx * sx);
-        g.Mrr = cr * cr * iu + sr * sr * iv;
-        g.Mcc = sr * sr * iu + cr * cr * iv;
-        g.Mrc = sr * cr * (iv - iu);
-        const float hl = 0.72134752f;  // log2(e) / 2
-        c.A = -hl * g.Mcc;
-        c.C = -hl * g.Mrr;
-        c.B = -2.f * hl * g.Mrc;
-        {
-          const bool blocks = amp > 0.f && c.C >= -2.f && isfinite(c.A) && isfinite(c.B) && isfinite(c.C);
-          c.la = blocks ? log2f(amp) : amp;
-          c.k2 = blocks ? exp2f(2.f * c.C) : -1.f;
-          c.k3 = blocks ? exp2f(6.f * c.C) : -1.f;
-          c.pad[0] = c.pad[1] = 0;
-        }
-        const double yr = rint(yd), xr = rint(xd);
-        c.irf = (float)yr;
-        c.fr = (float)(yd - yr);
-        c.icf = (float)xr;
-        c.fc = (float)(xd - xr);
-        g.x = (float)xd;
-        g.y = (float)yd;
-        g.T2 = 2.f * logf(fabsf(amp) / tau);
-        g.det = g.Mrr * g.Mcc - g.Mrc * g.Mrc;
-        const float inv_det = 1.f / g.det, inv_rr = 1.f / g.Mrr;
-        g.inv_cc = 1.f / g.Mcc;
-        const float er = sqrtf(g.T2 * g.Mcc * inv_det);
-        g.ec = sqrtf(g.T2 * g.Mrr * inv_det);
-        g.degenerate = !(isfinite(er) && isfinite(g.ec));
-        g.inv_rr = inv_rr;
-        g.pad0 = 0.f;
-        const float lo_r = fmaxf(floorf(g.y - er) - 1.f, 0.f), hi_r = fminf(ceilf(g.y + er) + 1.f, N - 1.f);
-        const float lo_c = fmaxf(floorf(g.x - g.ec) - 1.f, 0.f), hi_c = fminf(ceilf(g.x + g.ec) + 1.f, N - 1.f);
-        if (g.degenerate) {
-          live = true;
-          c.r0 = 0; c.r1 = N - 1; c.c0 = 0; c.c1 = N - 1;
-        } else if (lo_r <= hi_r && lo_c <= hi_c) {
-          live = true;
-          c.r0 = (int)lo_r; c.r1 = (int)hi_r; c.c0 = (int)lo_c; c.c1 = (int)hi_c;
-        }
-        g.ka = fabsf(amp) * 1.0001f;
-        g.kx = (g.det * inv_rr) * 0.9999f * hl;
-        g.ky = (g.det * g.inv_cc) * 0.9999f * hl;
-        g.pad = 0.f;
-        // the pixel nearest to the centre is at most half a pixel away in each coordinate:
-        // this slot alone lifts it above the threshold -> the > 0.01 mask is not empty
-        const float qmax = 0.25f * (g.Mrr + g.Mcc + 2.f * fabsf(g.Mrc));
-        if (amp * __expf(-0.5f * qmax) > 0.0101f && g.x >= 0.f && g.x <= N - 1.f && g.y >= 0.f &&
-            g.y <= N - 1.f)
-          certified = true;
-      }
-      if (p[0] < 0.0) all_nonneg = false;
-    }
-    const unsigned mask = __ballot_sync(0xffffffffu, live);
-    if (live) {
-      const int pos = base + __popc(mask & ((1u << lane) - 1u));
-      sm.coef[cb][pos] = c;
-      geo[pos] = g;
-    }
-    base += __popc(mask);
-  }
-  __syncwarp();
-  RSB_BSTAMP(1);
-  RSB_BSTAMP(2);
-  // Zoom images only use the crop [margin, N-margin)^2 of the raw image, and margin >= dlo,
-  // where dlo is a border distance d such that an UPPER BOUND of the image over the frame
-  // {border distance <= d - 1} stays below the 0.01 threshold.  Bound: sum over slots of the
-  // slot's maximum over the frame = amp if its centre lies in the frame, else amp * exp(-q/2)
-  // with q the smallest Mahalanobis distance to the four frame lines.  The bound grows with d:
-  // 32 frames are tried at once, one per lane (dlo only feeds the tile skip, a multiple of
-  // `step` is as good as the exact value).
-  int dlo = 0;
-  all_nonneg = __all_sync(0xffffffffu, all_nonneg);
-  if (zoom) {
-    certified = __any_sync(0xffffffffu, certified) && all_nonneg;
-    // without the certificate an empty mask (margin := 0, whole image used) cannot be ruled out
-    if (certified) {
-      const int half = (N - 1) / 2, step = (half + 31) / 32;
-      const int d = step * lane + step - 1;
-      const float lo = (float)d, hi = (float)(N - 1 - d);
-      float u = 0.f;
-#pragma unroll 4
-      for (int pos = 0; pos < base; ++pos) {  // branch-free: the exponentials of a batch overlap
-        const float4 gx = *reinterpret_cast<const float4*>(&geo[pos].ec);   // ec x y det
-        const float4 gk = *reinterpret_cast<const float4*>(&geo[pos].ka);   // ka kx ky -
-        const bool in_frame = gx.y <= lo || gx.y >= hi || gx.z <= lo || gx.z >= hi;
-        const float dc0 = lo - gx.y, dc1 = hi - gx.y, dr0 = lo - gx.z, dr1 = hi - gx.z;
-        const float q = fminf(fminf(dc0 * dc0, dc1 * dc1) * gk.y, fminf(dr0 * dr0, dr1 * dr1) * gk.z);
-        u += gk.x * ex2(in_frame ? 0.f : -q);
-      }
-      const unsigned okm = __ballot_sync(0xffffffffu, d <= half && u <= 0.00999f);
-      const unsigned bad = ~okm;
-      const int lead = bad ? lowest_bit(bad) : 32;  // leading frames that hold nothing above the threshold
-      dlo = (lead == 32) ? 0 : step * lead;         // (all 32 below: cannot happen with a certificate; stay safe)
-    }
-  }
-  if (lane == 0) {
-    sm.nlive[cb] = base;
-    // float32 noise of a rendered pixel near the 0.01 threshold.  All amplitudes >= 0: every
-    // term's error is relative to the term (<= 3e-5: SFU 2^-22 per factor, argument rounding
-    // with cancellation, accumulation), so the sum's is relative to the pixel value; plus
-    // the tails dropped by the footprint cut (slots x tau).  Otherwise: relative to the
-    // largest amplitude.
-    sm.delta[cb] = all_nonneg ? 3e-7f + 4e-7f * amax : 6e-6f * fmaxf(1.f, amax);
-    sm.dlo[cb] = dlo;
-  }
-  RSB_BSTAMP(3);
-  // ---- static work lists -------------------------------------------------------------
-  // Every tile's set of overlapping slots is known here, one image ahead of its use, so the
-  // tiles are dealt to the warps now: sorted by cost (slots hit), heaviest first, in snake
-  // order.  The renderers then read their list with plain loads -- no queue, no atomics, no
-  // shuffles on their critical path.  Warps 0 and 1 (side jobs) receive none.
-  {
-    uint2* rec = &sm.rec[cb][0][0];
-    for (int e = lane; e < kWarps * kMaxRec; e += 32) rec[e] = make_uint2(0u, kRecEnd);
-    __syncwarp();
-    unsigned hits[TPL];
-    int cost[TPL], tag[TPL], among[TPL];
-#pragma unroll
-    for (int h = 0; h < TPL; ++h) { hits[h] = 0u; cost[h] = tag[h] = among[h] = 0; }
-#pragma unroll
-    for (int h = 0; h < TPL; ++h) {
-      const int u = lane + 32 * h;
-      if (u < ntiles) {
-        const unsigned inv_tc = (65536u + (unsigned)tcols - 1u) / (unsigned)tcols;
-        const int g = (int)(((unsigned)u * inv_tc) >> 16), tc = u - g * tcols;
-        const int r0 = R0 + g * kTileRows, tc0 = tc * kTileCols;
-        const int rend = min(R0 + H, r0 + kTileRows);
-        // every pixel of the tile closer than dlo to the border: never read, never above 0.01
-        // (two pixels of slack: zero-weight taps may touch the crop's neighbours)
-        const int rmid = min(max(N >> 1, r0), rend - 1), cmid = min(max(N >> 1, tc0), min(tc0 + kTileCols, N) - 1);
-        const int far = min(min(rmid, N - 1 - rmid), min(cmid, N - 1 - cmid));
-        if (!(zoom && far < dlo - 2)) {
-          // a slot touches the tile when its > tau ellipse  M[dr,dc] <= T^2  meets the tile's
-          // rectangle (1.5 pixels of slack): the form's minimum over a box that does not hold
-          // the centre lies on one of the four edges.  No square roots, no divisions.
-          const float ra = (float)r0 - 1.5f, rb = (float)(rend - 1) + 1.5f;
-          const float ca = (float)tc0 - 1.5f, cb_ = (float)(min(tc0 + kTileCols, N) - 1) + 1.5f;
-          unsigned m = 0u;
-#pragma unroll 4
-          for (int pos = 0; pos < base; ++pos) {  // branch-free: the loads of a batch overlap
-            const int2 bbr = *reinterpret_cast<const int2*>(&sm.coef[cb][pos].r0);  // r0 r1
-            const int2 bbc = *reinterpret_cast<const int2*>(&sm.coef[cb][pos].c0);  // c0 c1
-            const int4 bb = make_int4(bbr.x, bbr.y, bbc.x, bbc.y);
-            const float4 gm = *reinterpret_cast<const float4*>(&geo[pos].Mrr);     // Mrr Mcc Mrc T2
-            const float4 gx = *reinterpret_cast<const float4*>(&geo[pos].ec);      // ec x y det
-            const float4 gi = *reinterpret_cast<const float4*>(&geo[pos].inv_cc);  // inv_cc inv_rr - -
-            const bool inbox = !(bb.y < r0 || bb.x >= rend || bb.w < tc0 || bb.z >= tc0 + kTileCols);
-            const float dra = ra - gx.z, drb = rb - gx.z, dca = ca - gx.y, dcb = cb_ - gx.y;
-            // only the edges that face the centre can hold the minimum
-            const bool use_c = dca > 0.f || dcb < 0.f, use_r = dra > 0.f || drb < 0.f;
-            const float e = dca > 0.f ? dca : dcb, f = dra > 0.f ? dra : drb;
-            const float tc_ = fminf(fmaxf(-gm.z * e * gi.y, dra), drb);  // column edge dc = e, dr free
-            const float qc = (gm.x * tc_ + 2.f * gm.z * e) * tc_ + gm.y * e * e;
-            const float tr_ = fminf(fmaxf(-gm.z * f * gi.x, dca), dcb);  // row edge dr = f, dc free
-            const float qr = (gm.y * tr_ + 2.f * gm.z * f) * tr_ + gm.x * f * f;
-            const float big = 3.0e38f;
-            float qmin = fminf(use_c ? qc : big, use_r ? qr : big);
-            if (!use_c && !use_r) qmin = 0.f;  // the centre lies inside the rectangle
-            // (NaN from a degenerate slot counts as touching)
-            if (inbox && !(qmin > gm.w)) m |= 1u << pos;
-          }
-          hits[h] = m;
-          cost[h] = 1 + min(__popc(hits[h]), 30);
-          tag[h] = (g << 8) | tc;
-          among[h] = atomicAdd(&sm.hist[cost[h]], 1);  // position among the tiles of equal cost
-        }
-      }
-    }
-    __syncwarp();
-    // rank = tiles of higher cost + position among equals
-    int above[TPL];
-#pragma unroll
-    for (int h = 0; h < TPL; ++h) above[h] = 0;
-    for (int c = 31; c >= 1; --c) {
-      const int n = sm.hist[c];
-#pragma unroll
-      for (int h = 0; h < TPL; ++h)
-        if (c > cost[h]) above[h] += n;
-    }
-    // Snake deal over the warps without a side job: first_worker .. kWarps - 1.
-    const int seats = kWarps - first_worker;
-#pragma unroll
-    for (int h = 0; h < TPL; ++h) {
-      if (cost[h] == 0) continue;
-      const int i = above[h] + among[h];
-      int ps = (i >= seats) + (i >= 2 * seats) + (i >= 3 * seats) + (i >= 4 * seats) + (i >= 5 * seats);
-      if constexpr (TPL > 2) ps += (i >= 6 * seats) + (i >= 7 * seats);
-      const int j = i - ps * seats;
-      const int w = first_worker + ((ps & 1) ? j : seats - 1 - j), e = ps;
-      sm.rec[cb][w][e] = make_uint2(hits[h], (unsigned)tag[h]);
-    }
-  }
-  RSB_BSTAMP(4);
-}
-
 // ---- float64 peak (jet_max) for the labels, one warp -------------------------------
 // The float32 image fixes WHERE the maximum is; its float64 value is recomputed from the
 // parameters: the raw pixels under the non-zero taps (<= 3 x 3) x slots, operation order of
@@ -736,17 +509,9 @@ __device__ inline Tap3 merge_taps(const Taps64& t, int N) {
   return m;
 }
 
-// kVar: every image has its own size (a.sizes[img] <= a.size) and output offset -- the sub-jets
-// of a survey (reference survey/survey.py:54-60) in ONE launch.  With two CTAs per image the
-// first band takes ceil(N/2) rows, so odd sizes work: the centre row (N-1)/2 is the last row of
-// the first band and the halo row of the second, and no tap with a non-zero weight reaches
-// further across (the composite operator preserves the centre).
-// kBig (one CTA per image only): the whole image of up to 224 rows sits in this CTA's shared memory.  The V
-// pass cannot keep that many rows in registers, so it runs twice -- once for the maximum, once to scale and
-// store -- which costs less than the second CTA's barriers and exchanges for images of 129 .. 224 pixels.
-template <int kCluster, int NS, bool kVar = false, bool kBig = false>
+template <int kCluster, int NS>
 __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
-  static_assert(!kBig && !kVar && kCluster >= 2 && kCluster <= 8, "band kernel: 2..8 CTAs per image, fixed size");
+  static_assert(kCluster >= 2 && kCluster <= 8 && NS <= 4, "band kernel: 2..8 CTAs per image, up to 512 columns");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Fixed2& sm = *reinterpret_cast<Fixed2*>(smem_raw);
   const int slots = a.slots;
@@ -762,7 +527,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
   const bool f64 = (a.flags & RSB_JET_OUT_F64) != 0;
   const bool normalize = (a.flags & RSB_JET_NORMALIZE) != 0;
   const size_t esz = f64 ? 8 : 4;
-  // ---- geometry of the current image (fixed for the whole launch unless kVar) ----
+  // ---- geometry of the image (fixed for the whole launch) ----
   int N, npad, pitch, opitch;  // size, size rounded up to 4, raw row pitch, output row pitch (elements)
   int Hb, H, R0, base;         // rows per band, rows of THIS band, its first absolute row (= base: raw row 0)
   int strips, tcols, stage_rows;
@@ -855,8 +620,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
   const int first_worker = (rank == 0) ? 2 : 1;
   if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
-    if constexpr (kBig) build_coefs2_big<4>(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker);
-    else build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker, kCluster, rank);
+    build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker, kCluster, rank);
   }
   // the peer CTA is resident and its mbarriers are initialised before any st.async
   if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
@@ -888,9 +652,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       bulk_s2g(const_cast<char*>(bulk_dst), stage, bulk_bytes);
       bulk_dst = nullptr;
     }
-    if constexpr (kVar) {
-      if (it > 0) geometry(a.sizes[img]);
-    }
     if (tid == 0) {  // running reductions of this image (all reads of the previous values are behind A)
       sm.lbest = 0ull;
       sm.lmargin = N;
@@ -906,19 +667,8 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
         if (img + nclusters < a.n) {
           const int nb = (it + 1) % 3;
           mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
-          int nN = N, nR0 = R0, nH = H;  // the next image's geometry
-          if constexpr (kVar) {
-            nN = a.sizes[img + nclusters];
-            const int g0 = (kCluster == 1) ? nN : (nN + 1) / 2;
-            nH = (kCluster == 1 || rank == 0) ? g0 : nN - g0;
-            nR0 = (rank == 0) ? 0 : g0;
-          }
-          if constexpr (kBig)
-            build_coefs2_big<4>(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane,
-                                a.zoom_pad[img + nclusters] >= 0, first_worker);
-          else
-            build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane,
-                         a.zoom_pad[img + nclusters] >= 0, first_worker, kCluster, rank);
+          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, N, R0, H, lane, a.zoom_pad[img + nclusters] >= 0,
+                       first_worker, kCluster, rank);
         }
         RSB_STAMP_T(12, kCoefWarp * 32);
       } else if (warp == kLabelWarp) {
@@ -1246,7 +996,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
     RSB_STAMP(1);  // this warp is out of tiles
     int margin = 0;
     char* out = reinterpret_cast<char*>(a.out) +
-                (kVar ? (size_t)a.out_offs[img] : (size_t)img * N * N) * esz;
+                (size_t)img * N * N * esz;
     unsigned long long image_best = 0ull;  // arg-max key of the final image (normalize only)
 
     if (!zoom) {
@@ -1336,7 +1086,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       const int flo = sm.foot_lo, fhi = sm.foot_hi;  // empty footprint: flo = N, fhi = -1
 
 
-      int dbg_rows_out = 0;
       // H pass, in place: row r of raw becomes row r of T.  Rows are dealt statically; lane <-> ADJACENT
       // columns (c = strip + 32 j + lane): a warp's gathers touch consecutive words (composite stride <= 2).
       // With up to four strips the tap records (16 per lane) do not stay in registers: they come from the
@@ -1409,64 +1158,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
         const int g = row >> 3, owner = g % kCluster, lr = ((g / kCluster) << 3) + (row & 7);
         return cluster_map(raw_off + (uint32_t)(lr * pitch) * 4u, (uint32_t)owner);
       };
-      if constexpr (kBig) {
-        // V pass twice: the maximum first, then the same values again, scaled and stored
-        auto vrow = [&](int r, int s) -> float4 {   // four output pixels of row r, strip s (zeros off the footprint)
-          const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
-          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (r < vr0 || r > vr1 || !(s < strips && sc0 <= fhi && sc0 + kStrip - 1 >= flo) || c0 >= N) return v;
-          const float4 tp = lds_v4(s_tab + (uint32_t)r * 16u);
-          const int l0 = __float_as_int(tp.w);
-          // (zero-weight taps are clamped into the crop: only its rows hold T)
-          const uint32_t p0 = s_raw + (uint32_t)(min(max(l0, tlo), thi) * pitch + c0) * 4u;
-          const uint32_t p1 = s_raw + (uint32_t)(min(max(l0 + 1, tlo), thi) * pitch + c0) * 4u;
-          const uint32_t p2 = s_raw + (uint32_t)(min(max(l0 + 2, tlo), thi) * pitch + c0) * 4u;
-          const float4 t0 = lds_v4(p0), t1 = lds_v4(p1), t2 = lds_v4(p2);
-          const f2 W0 = f2_pack(tp.x, tp.x), W1 = f2_pack(tp.y, tp.y), W2 = f2_pack(tp.z, tp.z);
-          f2_unpack(f2_fma(W2, f2_pack(t2.x, t2.y), f2_fma(W1, f2_pack(t1.x, t1.y), f2_mul(W0, f2_pack(t0.x, t0.y)))), v.x, v.y);
-          f2_unpack(f2_fma(W2, f2_pack(t2.z, t2.w), f2_fma(W1, f2_pack(t1.z, t1.w), f2_mul(W0, f2_pack(t0.z, t0.w)))), v.z, v.w);
-          return v;
-        };
-        float inv = 1.f;
-        if (normalize) {
-          best_v = -1.f;
-          best_i = 0;
-          for (int r = vr0 + warp; r <= vr1; r += kWarps) {
-#pragma unroll
-            for (int s = 0; s < NS; ++s) {
-              const int c0 = s * kStrip + 4 * lane;
-              if (s >= strips || c0 >= N) continue;
-              float4 m = vrow(r, s);
-              if (c0 + 3 >= N) {  // ragged last group: columns >= N do not take part
-                if (c0 + 1 >= N) m.y = -1.f;
-                if (c0 + 2 >= N) m.z = -1.f;
-                m.w = -1.f;
-              }
-              const float top = fmaxf(fmaxf(m.x, m.y), fmaxf(m.z, m.w));
-              const int pi = r * N + c0 + (m.x == top ? 0 : (m.y == top ? 1 : (m.z == top ? 2 : 3)));
-              if (top > best_v || (top == best_v && pi < best_i)) {
-                best_v = top;
-                best_i = pi;
-              }
-            }
-          }
-          my_best = warp_max_u64(best_v >= 0.f ? best_key(best_v, best_i) : 0ull);
-          if (lane == 0) atomicMax(&sm.lbest, my_best);
-          worker_sync();
-          image_best = sm.lbest;
-          inv = 1.f / __uint_as_float((unsigned)(image_best >> 32));
-        }
-        for (int r = R0 + warp; r < R0 + H; r += kWarps) {
-#pragma unroll
-          for (int s = 0; s < NS; ++s) {
-            const int c0 = s * kStrip + 4 * lane;
-            if (s >= strips || c0 >= N) continue;
-            float4 v = vrow(r, s);
-            v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
-            store_out4(out + (size_t)r * opitch * esz, f64, c0, N, vec, v);
-          }
-        }
-      } else {
       // V pass: results stay in registers (<= 8 rows x NS strips of 4 columns per lane)
       float4 res[kRowsPerWarp][NS];
       // running maximum of this lane: value and pixel index (its pixels come in increasing
@@ -1563,7 +1254,6 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
           }
         }
       }
-      }  // !kBig
     }
     if (stage_rows > 0) {
       fence_proxy_async();  // my writes to the stage -> visible to the async (TMA) proxy
