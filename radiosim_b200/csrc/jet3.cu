@@ -1158,51 +1158,90 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
         const int g = row >> 3, owner = g % kCluster, lr = ((g / kCluster) << 3) + (row & 7);
         return cluster_map(raw_off + (uint32_t)(lr * pitch) * 4u, (uint32_t)owner);
       };
-      // V pass: results stay in registers (<= 8 rows x NS strips of 4 columns per lane)
+      // V pass: results stay in registers (4 rows x NS strips of 4 columns per lane).  A warp owns four
+      // CONSECUTIVE output rows (half of one of this CTA's 8-row groups): their tap rows overlap, so the
+      // union of them -- 3 k + 3 rows for a composite stride k, against 12 -- is fetched once through
+      // distributed shared memory and every fetched row is accumulated into the output rows that use it.
+      // Taps are visited in increasing row order, i.e. in each output's own tap order: same sums as
+      // fma(w2, t2, fma(w1, t1, w0 t0)).
       float4 res[kRowsPerWarp][NS];
       // running maximum of this lane: value and pixel index (its pixels come in increasing
       // index order, so '>' keeps the first of equal values)
       best_v = -1.f;
       best_i = 0;
+      auto my_row = [&](int i) -> int { return ((warp >> 1) << 3) + ((warp & 1) << 2) + i; };  // local row
+      {
+        int tb[kRowsPerWarp];            // first tap row of each output row (absolute)
+        float tw[kRowsPerWarp][3];       // its three weights (all zero: row off the footprint)
+        int umin = 0x7fffffff, umax = -1;
 #pragma unroll
-      for (int i = 0; i < kRowsPerWarp; ++i) {
-        const int lr = warp + i * kWarps, r = abs_row(lr);
+        for (int i = 0; i < kRowsPerWarp; ++i) {
+          const int lr = my_row(i), r = abs_row(lr);
 #pragma unroll
-        for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (lr >= H || r < vr0 || r > vr1) continue;  // warp-uniform
-        const float4 tp = lds_v4(s_tab + (uint32_t)r * 16u);
-        const float w0 = tp.x, w1 = tp.y, w2 = tp.z;
-        // only zero-weight taps can fall outside the crop: clamp them onto rows that hold T (0 x whatever an
-        // unrendered tile left behind must not become NaN).  The rows may be any CTA's.
-        const int l0 = __float_as_int(tp.w);
-        const uint32_t p0 = t_row(min(max(l0, tlo), thi));
-        const uint32_t p1 = t_row(min(max(l0 + 1, tlo), thi));
-        const uint32_t p2 = t_row(min(max(l0 + 2, tlo), thi));
+          for (int s = 0; s < NS; ++s) res[i][s] = make_float4(0.f, 0.f, 0.f, 0.f);
+          tb[i] = 0;
+          tw[i][0] = tw[i][1] = tw[i][2] = 0.f;
+          if (lr < H && r >= vr0 && r <= vr1) {  // warp-uniform
+            const float4 tp = lds_v4(s_tab + (uint32_t)r * 16u);
+            tb[i] = __float_as_int(tp.w);
+            tw[i][0] = tp.x; tw[i][1] = tp.y; tw[i][2] = tp.z;
+            // (taps with a non-zero weight lie in the crop [tlo, thi]: only those are fetched)
 #pragma unroll
-        for (int s = 0; s < NS; ++s) {
-          const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
-          if (!(s < strips && sc0 <= fhi && sc0 + kStrip - 1 >= flo) || c0 >= N) continue;
-          const float4 t0 = ldc_v4(p0 + (uint32_t)c0 * 4u);
-          const float4 t1 = ldc_v4(p1 + (uint32_t)c0 * 4u);
-          const float4 t2 = ldc_v4(p2 + (uint32_t)c0 * 4u);
-          float4 v;
-          {
-            const f2 W0 = f2_pack(w0, w0), W1 = f2_pack(w1, w1), W2 = f2_pack(w2, w2);
-            f2_unpack(f2_fma(W2, f2_pack(t2.x, t2.y), f2_fma(W1, f2_pack(t1.x, t1.y), f2_mul(W0, f2_pack(t0.x, t0.y)))), v.x, v.y);
-            f2_unpack(f2_fma(W2, f2_pack(t2.z, t2.w), f2_fma(W1, f2_pack(t1.z, t1.w), f2_mul(W0, f2_pack(t0.z, t0.w)))), v.z, v.w);
+            for (int t = 0; t < 3; ++t)
+              if (tw[i][t] != 0.f) {
+                umin = min(umin, tb[i] + t);
+                umax = max(umax, tb[i] + t);
+              }
           }
-          res[i][s] = v;
-          if (normalize) {
-            float4 m = v;
-            if (c0 + 3 >= N) {  // ragged last group: columns >= N do not take part
-              if (c0 + 1 >= N) m.y = -1.f;
-              if (c0 + 2 >= N) m.z = -1.f;
-              m.w = -1.f;
+        }
+        umin = max(umin, tlo);
+        umax = min(umax, thi);
+        for (int u = umin; u <= umax; ++u) {
+          float wu[kRowsPerWarp];
+          bool any = false;
+#pragma unroll
+          for (int i = 0; i < kRowsPerWarp; ++i) {
+            const int o = u - tb[i];
+            wu[i] = (o == 0) ? tw[i][0] : (o == 1) ? tw[i][1] : (o == 2) ? tw[i][2] : 0.f;
+            any = any || wu[i] != 0.f;
+          }
+          if (!any) continue;  // (a gap between two output rows' taps)
+          const uint32_t pu = t_row(u);
+#pragma unroll
+          for (int s = 0; s < NS; ++s) {
+            const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
+            if (!(s < strips && sc0 <= fhi && sc0 + kStrip - 1 >= flo) || c0 >= N) continue;
+            const float4 t = ldc_v4(pu + (uint32_t)c0 * 4u);
+            const f2 tlo2 = f2_pack(t.x, t.y), thi2 = f2_pack(t.z, t.w);
+#pragma unroll
+            for (int i = 0; i < kRowsPerWarp; ++i) {
+              const f2 W = f2_pack(wu[i], wu[i]);
+              float4& v = res[i][s];
+              f2_unpack(f2_fma(W, tlo2, f2_pack(v.x, v.y)), v.x, v.y);
+              f2_unpack(f2_fma(W, thi2, f2_pack(v.z, v.w)), v.z, v.w);
             }
-            const float top = fmaxf(fmaxf(m.x, m.y), fmaxf(m.z, m.w));
-            if (top > best_v) {
-              best_v = top;
-              best_i = r * N + c0 + (m.x == top ? 0 : (m.y == top ? 1 : (m.z == top ? 2 : 3)));
+          }
+        }
+        if (normalize) {
+#pragma unroll
+          for (int i = 0; i < kRowsPerWarp; ++i) {
+            const int lr = my_row(i), r = abs_row(lr);
+            if (lr >= H || r < vr0 || r > vr1) continue;
+#pragma unroll
+            for (int s = 0; s < NS; ++s) {
+              const int sc0 = s * kStrip, c0 = sc0 + 4 * lane;
+              if (!(s < strips && sc0 <= fhi && sc0 + kStrip - 1 >= flo) || c0 >= N) continue;
+              float4 m = res[i][s];
+              if (c0 + 3 >= N) {  // ragged last group: columns >= N do not take part
+                if (c0 + 1 >= N) m.y = -1.f;
+                if (c0 + 2 >= N) m.z = -1.f;
+                m.w = -1.f;
+              }
+              const float top = fmaxf(fmaxf(m.x, m.y), fmaxf(m.z, m.w));
+              if (top > best_v) {
+                best_v = top;
+                best_i = r * N + c0 + (m.x == top ? 0 : (m.y == top ? 1 : (m.z == top ? 2 : 3)));
+              }
             }
           }
         }
@@ -1226,7 +1265,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
         // float32, 16-byte aligned rows: the common case, kept free of the general store's branches
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
-          const int rl = warp + i * kWarps;
+          const int rl = my_row(i);
           if (rl < H) {
             float* outf = reinterpret_cast<float*>(out) + (size_t)abs_row(rl) * opitch + 4 * lane;
 #pragma unroll
@@ -1241,7 +1280,7 @@ __global__ void __launch_bounds__(kThreads, 1) jet3_kernel(const Args a) {
       } else {
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
-          const int rl = warp + i * kWarps;
+          const int rl = my_row(i);
           if (rl >= H) continue;
           const int r = abs_row(rl);
 #pragma unroll
