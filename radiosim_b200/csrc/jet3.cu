@@ -1372,8 +1372,7 @@ bool v3_supported(int size, int slots, size_t* smem_bytes) {
 int v3_launch(const Args& a_in, size_t smem_bytes, cudaStream_t st) {
   Args a = a_in;
   a.stage_rows = (int)((smem_bytes - v3_bytes(a.size, 0)) / ((size_t)((a.size + 3) & ~3) * 4));
-  const int strips = (a.size + kStrip - 1) / kStrip;  // 3 or 4 for 257 .. 512
-  return strips <= 3 ? v3::launch_v3<kV3Cluster, 3>(a, smem_bytes, st) : v3::launch_v3<kV3Cluster, 4>(a, smem_bytes, st);
+  return v3::launch_v3<kV3Cluster, 4>(a, smem_bytes, st);  // four 128-column strips for 401 .. 512
 }
 
 }  // namespace jet
