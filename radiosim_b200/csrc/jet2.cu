@@ -58,6 +58,7 @@ constexpr int kMaxCand = 64;
 constexpr int kMaxTiles = kMaxGroups * 4;  // 64-column tiles of a band (size <= 256)
 constexpr int kMaxRec = 8;                 // tiles per warp and image (work list length)
 constexpr unsigned kRecEnd = 0xffffu;      // list terminator in rec.y
+constexpr int kListCap = 512;              // images of one launch a cluster can list (else: plain striding)
 
 // float32 coefficients of one live component as the tile loop reads them (warp-uniform):
 //   g(r,c) = 2^(la + A dc^2 + B dc dr + C dr^2),  dc = c - (icf + fc), dr = r - (irf + fr)
@@ -98,6 +99,9 @@ struct __align__(16) Fixed2 {
   int ncand;                        // borderline pixels awaiting a float64 verdict
   int cand[kMaxCand];               // r << 16 | c
   uint2 rec[2][kWarps][kMaxRec];    // per-warp work lists: {slots that touch the tile, row group << 8 | column tile}
+  int img_list[kListCap];           // this cluster's images: the zoom ones, then the plain ones
+  int nimg;                         // ... how many
+  int wz[kWarps], wp[kWarps];       // (building it: zoom / plain images per warp's range)
 };
 
 // one slot's float64 value at a raw pixel, operation order of gauss.py:77-88
@@ -853,25 +857,80 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     sm.next_row = 0;
   }
   __syncthreads();
+  // ---- which images this cluster renders --------------------------------------------------------------
+  // A zoom image costs ~1.8 x a plain one, so striding through the batch gives the clusters unequal sums (the
+  // slowest of 74 ends ~3 % behind the mean at 16 384 images).  Instead the zoom images of the launch are dealt
+  // round-robin to the clusters, and the plain ones round-robin from the other end: every cluster gets the same
+  // number of each (+- 1).  Both CTAs of a cluster build the same list.
+  // (the launcher keeps a.n <= kListCap x clusters; everything below the list lives in shared memory, not in
+  // registers: the render loops have none to spare)
+  {
+    const int per = ((a.n + kWarps * 32 - 1) / (kWarps * 32)) * 32;  // images per warp (a multiple of 32)
+    const int lo = min(a.n, warp * per), hi = min(a.n, lo + per);
+    int zc = 0, pc = 0;
+    for (int b0 = lo; b0 < hi; b0 += 32) {
+      const int i = b0 + lane;
+      const bool v = i < hi, z = v && a.zoom_pad[i] >= 0;
+      zc += __popc(__ballot_sync(0xffffffffu, z));
+      pc += __popc(__ballot_sync(0xffffffffu, v && !z));
+    }
+    if (lane == 0) {
+      sm.wz[warp] = zc;
+      sm.wp[warp] = pc;
+    }
+    __syncthreads();
+    int z0 = 0, p0 = 0, Z = 0, P = 0;
+    for (int w = 0; w < kWarps; ++w) {
+      if (w < warp) { z0 += sm.wz[w]; p0 += sm.wp[w]; }
+      Z += sm.wz[w];
+      P += sm.wp[w];
+    }
+    const int back = nclusters - 1 - cid;  // the plain images are dealt from the other end
+    const int nz = Z > cid ? (Z - cid + nclusters - 1) / nclusters : 0;
+    if (tid == 0) sm.nimg = nz + (P > back ? (P - back + nclusters - 1) / nclusters : 0);
+    const unsigned lt = (1u << lane) - 1u;
+    for (int b0 = lo; b0 < hi; b0 += 32) {
+      const int i = b0 + lane;
+      const bool v = i < hi, z = v && a.zoom_pad[i] >= 0;
+      const unsigned mz = __ballot_sync(0xffffffffu, z), mp = __ballot_sync(0xffffffffu, v && !z);
+      if (z) {
+        const int r = z0 + __popc(mz & lt);
+        if (r % nclusters == cid) sm.img_list[r / nclusters] = i;
+      } else if (v) {
+        const int r = p0 + __popc(mp & lt);
+        if (r % nclusters == back) sm.img_list[nz + r / nclusters] = i;   // (zoom ones first, then the plain ones)
+      }
+      z0 += __popc(mz);
+      p0 += __popc(mp);
+    }
+    __syncthreads();
+  }
+  const uint32_t s_list = smem_u32(&sm.img_list[0]), s_nimg = smem_u32(&sm.nimg);
+  auto image_at = [&](int k) -> int { return lds_s32(s_list + (uint32_t)k * 4u); };  // k < images()
+  auto images = [&]() -> int { return lds_s32(s_nimg); };
   auto prefetch = [&](int image, int pb) {  // one thread: parameter block -> params[pb]
     fence_proxy_async();
     mbar_expect_tx(&sm.bar[pb], pbytes);
     bulk_g2s(sm.params[pb], a.params + (size_t)image * slots * 6, pbytes, &sm.bar[pb]);
   };
-  if (tid == 0 && cid < a.n) {
-    prefetch(cid, 0);
-    if (cid + nclusters < a.n) prefetch(cid + nclusters, 1);
+  const int img0 = images() > 0 ? image_at(0) : 0;
+  if constexpr (kVar) {
+    if (images() > 0) geometry(a.sizes[img0]);  // (the first image is no longer image number cid)
+  }
+  if (tid == 0 && images() > 0) {
+    prefetch(img0, 0);
+    if (images() > 1) prefetch(image_at(1), 1);
   }
   // warp 1 only has its side job (the labels) in the cluster's first CTA; elsewhere it renders
   const int first_worker = (rank == 0) ? 2 : 1;
-  if (warp == 0 && cid < a.n) {  // prologue: coefficients of the first image
+  if (warp == 0 && images() > 0) {  // prologue: coefficients of the first image
     mbar_wait(&sm.bar[0], 0);
-    if constexpr (kBig) build_coefs2_big<4>(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker);
-    else build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[cid] >= 0, first_worker);
+    if constexpr (kBig) build_coefs2_big<4>(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[img0] >= 0, first_worker);
+    else build_coefs2(sm, 0, sm.params[0], slots, N, R0, H, lane, a.zoom_pad[img0] >= 0, first_worker);
   }
   // the peer CTA is resident and its mbarriers are initialised before any st.async
   if constexpr (kCluster > 1) cg::this_cluster().sync(); else __syncthreads();
-  int zpad_next = (cid < a.n) ? a.zoom_pad[cid] : -1;
+  int zpad_next = (images() > 0) ? a.zoom_pad[img0] : -1;
 
   // Two warps start each image with a side job before they join the tile queue: warp 0 builds
   // the NEXT image's coefficients and culling spans, warp 1 turns the PREVIOUS image's arg-max
@@ -890,7 +949,9 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
   };
 
   int it = 0;
-  for (int img = cid; img < a.n; img += nclusters, ++it) {
+  for (; it < images(); ++it) {
+    const int img = image_at(it);
+    const int img_next = (it + 1 < images()) ? image_at(it + 1) : -1;  // (-1: this was the last one)
     const int buf = it & 1;   // coefficient / exchange-slot parity
     const int pb = it % 3;    // parameter buffer
     mbar_wait(&sm.bar[pb], (it / 3) & 1);
@@ -914,40 +975,40 @@ __global__ void __launch_bounds__(kThreads, 1) jet2_kernel(const Args a) {
     __syncwarp();
     {
       if (warp == kCoefWarp) {
-        if (img + nclusters < a.n) {
+        if (img_next >= 0) {
           const int nb = (it + 1) % 3;
           mbar_wait(&sm.bar[nb], ((it + 1) / 3) & 1);
           int nN = N, nR0 = R0, nH = H;  // the next image's geometry
           if constexpr (kVar) {
-            nN = a.sizes[img + nclusters];
+            nN = a.sizes[img_next];
             const int g0 = (kCluster == 1) ? nN : (nN + 1) / 2;
             nH = (kCluster == 1 || rank == 0) ? g0 : nN - g0;
             nR0 = (rank == 0) ? 0 : g0;
           }
 #ifdef RSB_TIMELINE
-          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane, a.zoom_pad[img + nclusters] >= 0,
+          build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane, a.zoom_pad[img_next] >= 0,
                        first_worker, g_timeline ? &g_timeline[((size_t)img * 2 + rank) * 96 + 24] : nullptr);
 #else
           if constexpr (kBig)
             build_coefs2_big<4>(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane,
-                                a.zoom_pad[img + nclusters] >= 0, first_worker);
+                                a.zoom_pad[img_next] >= 0, first_worker);
           else
             build_coefs2(sm, buf ^ 1, sm.params[nb], slots, nN, nR0, nH, lane,
-                         a.zoom_pad[img + nclusters] >= 0, first_worker);
+                         a.zoom_pad[img_next] >= 0, first_worker);
 #endif
         }
         RSB_STAMP_T(12, kCoefWarp * 32);
       } else if (warp == kLabelWarp) {
         // previous image's labels, then its parameter buffer is free for image it+2
         if (rank == 0 && it > 0) label_job(buf ^ 1);
-        if (lane == 0 && img + 2 * nclusters < a.n) prefetch(img + 2 * nclusters, (it + 2) % 3);
+        if (lane == 0 && it + 2 < images()) prefetch(image_at(it + 2), (it + 2) % 3);
         RSB_STAMP_T(13, kLabelWarp * 32);
       }
     }
     RSB_STAMP(0);
     const double* P = sm.params[pb];
     const int zpad = zpad_next;
-    if (img + nclusters < a.n) zpad_next = a.zoom_pad[img + nclusters];  // latency hidden
+    if (img_next >= 0) zpad_next = a.zoom_pad[img_next];  // latency hidden
     const bool zoom = zpad >= 0;
     const float thr = (float)kEdgeThr, delta = sm.delta[buf];
     const uint32_t s_coef = keep_u32(smem_u32(sm.coef[buf]));
@@ -1672,22 +1733,39 @@ static int launch_v2(const Args& a, size_t smem_bytes, cudaStream_t st) {
   const int sms = sm_count();
   // CTAs are limited to one per SM by registers (512 threads x 128); small images leave
   // shared memory for more, but the register file does not
-  int nclusters = sms / kCluster;
-  if (nclusters > a.n) nclusters = a.n;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(nclusters * kCluster));
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem_bytes;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kCluster;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  RSB_CUDA(cudaLaunchKernelEx(&cfg, k, a));
-  RSB_LAUNCHED();
+  const int full = sms / kCluster;
+  // a cluster lists its images of the launch in shared memory (kListCap entries): longer batches go in pieces
+  const int piece = (kListCap - 2) * full;
+  const size_t esz = (a.flags & RSB_JET_OUT_F64) ? 8 : 4;
+  for (int i0 = 0; i0 < a.n; i0 += piece) {
+    Args b = a;
+    b.n = (a.n - i0) < piece ? (a.n - i0) : piece;
+    b.params = a.params + (size_t)i0 * a.slots * 6;
+    b.zoom_pad = a.zoom_pad + i0;
+    b.margin = a.margin + i0;
+    b.peak = a.peak + i0;
+    if (kVar) {
+      b.sizes = a.sizes + i0;
+      b.out_offs = a.out_offs + i0;  // (offsets stay relative to a.out)
+    } else {
+      b.out = reinterpret_cast<char*>(a.out) + (size_t)i0 * a.size * a.size * esz;
+    }
+    const int nclusters = full < b.n ? full : b.n;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(nclusters * kCluster));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    RSB_CUDA(cudaLaunchKernelEx(&cfg, k, b));
+    RSB_LAUNCHED();
+  }
   return 0;
 }
 
