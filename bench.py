@@ -58,8 +58,9 @@ def shared_config(world):
         "workload": WORKLOAD, "img_size": SIZE, "slots": SLOTS, "num_jet_components": list(COMPS),
         "scaling": "normalize", "seed": "1337+rank (CUDA arm) / 4242+process (reference arm)",
         "parallelism": f"dp{world} (independent shards, no collective)",
-        "sweep": f"CUDA arm: {SWEEP} images per GPU per step in launches of {CHUNK}; "
-                 "reference arm: a bounded sample of the same workload per step",
+        "sweep": f"CUDA arm: {SWEEP} images per GPU per step in launches of {CHUNK} into a ring of two chunk "
+                 "buffers (launches alternate between two streams, so a chunk's tail runs under the next chunk's "
+                 "head); reference arm: a bounded sample of the same workload per step",
         "l2_policy": f"every launch writes {CHUNK * SIZE * SIZE * 4 / 2**20:.0f} MiB of images "
                      "(ring buffer in HBM) >> 126 MB L2",
     }
@@ -488,28 +489,41 @@ def run_cuda(args):
     flags = L.JET_NORMALIZE
     d_params = L.dev_from(jb.params)
     d_pad = L.dev_from(jb.zoom_pad)
-    d_img = L.DeviceBuffer(chunk * SIZE * SIZE * 4)          # the ring: every launch overwrites it
+    lanes = max(1, min(args.lanes, 4))
+    # the output ring: `lanes` chunk-sized slots, launch k renders into slot k % lanes on stream k % lanes, so the
+    # tail of one chunk (clusters that got the costlier images) runs under the head of the next
+    d_img = [L.DeviceBuffer(chunk * SIZE * SIZE * 4) for _ in range(lanes)]
     d_margin = L.DeviceBuffer(sweep * 4)
     d_peak = L.DeviceBuffer(sweep * 8)
     wsz = C.c_size_t(0)
     L.check(lib.rsb_jet_workspace_bytes(chunk, SLOTS, SIZE, C.byref(wsz)))
-    d_work = L.DeviceBuffer(max(wsz.value, 16))
-    stream = C.c_void_p()
-    L.check(lib.rsb_stream_create(C.byref(stream)))
-    ev = [C.c_void_p() for _ in range(2)]
+    d_work = [L.DeviceBuffer(max(wsz.value, 16)) for _ in range(lanes)]
+    streams = [C.c_void_p() for _ in range(lanes)]
+    for st in streams:
+        L.check(lib.rsb_stream_create(C.byref(st)))
+    stream = streams[0]
+    ev = [C.c_void_p() for _ in range(2 + lanes)]   # start, end, one "lane done" event per stream
     for e in ev:
         L.check(lib.rsb_event_create(C.byref(e)))
     starts = list(range(0, sweep, chunk))
 
     def step():
-        for i0 in starts:
+        for k, i0 in enumerate(starts):
             cnt = min(chunk, sweep - i0)
+            q = k % lanes
             L.check(lib.rsb_jet_render(d_params.ptr + i0 * SLOTS * 48, d_pad.ptr + i0 * 4, cnt, SLOTS, SIZE,
-                                       flags, d_img.ptr, d_margin.ptr + i0 * 4, d_peak.ptr + i0 * 8,
-                                       d_work.ptr, d_work.nbytes, stream), "rsb_jet_render")
+                                       flags, d_img[q].ptr, d_margin.ptr + i0 * 4, d_peak.ptr + i0 * 8,
+                                       d_work[q].ptr, d_work[q].nbytes, streams[q]), "rsb_jet_render")
+
+    def join_lanes():
+        """stream 0 waits for everything enqueued on the other streams so far"""
+        for q in range(1, lanes):
+            L.check(lib.rsb_event_record(ev[2 + q], streams[q]))
+            L.check(lib.rsb_stream_wait_event(streams[0], ev[2 + q]))
 
     def barrier():
-        L.check(lib.rsb_stream_sync(stream))
+        for st in streams:
+            L.check(lib.rsb_stream_sync(st))
         L.device_sync()
         if dist is not None:
             dist.barrier()
@@ -525,10 +539,11 @@ def run_cuda(args):
     barrier()
     launches0 = L.launch_count()
     t0 = time.perf_counter()
-    L.check(lib.rsb_event_record(ev[0], stream))
+    L.check(lib.rsb_event_record(ev[0], stream))       # (every stream is idle here: barrier() above)
     for _ in range(args.steps):
         step()
-    L.check(lib.rsb_event_record(ev[1], stream))
+    join_lanes()
+    L.check(lib.rsb_event_record(ev[1], stream))       # behind the last launch of every stream
     ms = C.c_float(0.0)
     L.check(lib.rsb_event_elapsed_ms(ev[0], ev[1], C.byref(ms)))
     barrier()
@@ -622,6 +637,7 @@ def run_cuda(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": cfg,
             "run": {"images_per_gpu_per_step": sweep, "launches_per_step": n_launch, "images_per_launch": chunk,
+                    "lanes": lanes,
                     "mean_live_components": live_all / (world * sweep), "zoom_fraction": zoom_frac,
                     "packer_images_per_s_per_core": pack_rate},
             "clocks": clocks,
@@ -699,6 +715,8 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--sweep", type=int, default=SWEEP, help="jets per GPU per step")
     ap.add_argument("--batch", type=int, default=CHUNK, help="jets per launch")
+    ap.add_argument("--lanes", type=int, default=2,
+                    help="slots of the output ring = streams the launches alternate between (1: one stream)")
     ap.add_argument("--e2e-batch", type=int, default=4096)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the C2-C4 records")
