@@ -79,8 +79,9 @@ int rsb_bench_sfu(int iters, double* ex2_per_second);
 #define RSB_JET_NORMALIZE 1u /* conf.jet.scaling == "normalize" (jet.py:177-181) */
 #define RSB_JET_OUT_F64 2u   /* out_img is float64 (the reference dtype), else float32 */
 
-/* Bytes of device scratch rsb_jet_render needs for n images of size x size
- * (0 when the image fits in shared memory). */
+/* Bytes of device scratch rsb_jet_render needs for n images of size x size: 0 when the raw image stays
+ * in shared memory -- up to 256 pixels (one CTA, or a 2-CTA cluster) and 401 .. 512 pixels (8-CTA cluster),
+ * with at most 32 slots; otherwise one scratch image per resident CTA. */
 int rsb_jet_workspace_bytes(int n, int slots, int size, size_t* bytes);
 
 /* Render n jets -- replaces, per image, component_from_list + plane sum
